@@ -1,0 +1,123 @@
+/* voxtrace.h — C ABI of the B200-native voxel ray-march path (libvoxtrace.so).
+ *
+ * Drop-in boundary for python_raytracer's CPU trace loop.  The reference has no FFI; its interface for this
+ * path is the Python object protocol of `Camera` (reference init.py:13-150).  Each entry point below names the
+ * reference interface it stands in for (paths relative to the reference root).  The Python mirror of that
+ * protocol (`python_raytracer_b200.GpuCamera`) is a thin ctypes layer over these calls; INTEGRATION.md shows
+ * the binding a maintainer of the reference would add.
+ *
+ * Conventions: every call returns 0 on success, non-zero on error; vt_last_error() then returns a host
+ * string owned by the context.  A context is bound to ONE CUDA device and ONE stream and is not
+ * thread-safe (the reference's Camera is likewise used by one caller at a time, init.py:205).
+ * Pointers named dev_* are device pointers on the context's device; host_* are host pointers.
+ * There is no CPU fallback: vt_create fails if no CUDA device is usable.
+ */
+#ifndef VOXTRACE_H
+#define VOXTRACE_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VT_ABI_VERSION 1
+#define VT_BRICK 8                 /* bricks are 8x8x8 cells = 512 bytes */
+#define VT_MAX_MATERIALS 255       /* material id 0 is "empty" */
+#define VT_RAY_RECORD 16           /* doubles per ray record (see vt_render) */
+
+typedef struct vt_ctx vt_ctx;
+
+/* Subset of `data.settings` the path reads (reference data.py:18-50) plus the derived fields of
+ * data.py:64-68.  Same names and meaning; `static_noise` is `settings.static`. */
+typedef struct {
+    int32_t width, height;         /* WINDOW width/height: the canvas the lens is defined on (init.py:131-132) */
+    int32_t samples;               /* RENDER samples (init.py:134) */
+    int32_t static_noise;          /* RENDER static: per-pixel streams do not change between frames (init.py:136) */
+    int32_t chunk_size;            /* RENDER chunk_size (init.py:68) */
+    int32_t chunk_radius;          /* round(chunk_size / 2) (data.py:68) */
+    int32_t background;            /* 0: data.background is None; 1: lib.material_background (init.py:119-120) */
+    int32_t reserved;
+    double shutter, falloff, dof, dist_min, dist_max, max_light, max_bounces;
+    double lod_bounces, lod_samples, lod_random, lod_edge;
+    double proportions;            /* ((w + h) / 2) / max(w, h) (data.py:66) */
+} vt_settings;
+
+/* One row of the structure-of-arrays material table: the optical fields `lib.material` reads
+ * (reference lib.py:448-460; mods/default/init.py:6-17).  Row 0 is unused (id 0 = empty cell). */
+typedef struct {
+    double albedo[3];              /* rgb 0..255 */
+    double roughness, absorption, ior, energy;
+    double reserved;
+} vt_material;
+
+/* ---- life cycle -------------------------------------------------------------------------------- */
+/* Camera.__init__ (init.py:14-18).  `device` is a CUDA ordinal. */
+int vt_create(int device, vt_ctx **out);
+void vt_destroy(vt_ctx *ctx);
+const char *vt_last_error(const vt_ctx *ctx);   /* ctx may be NULL: error of the last failed vt_create */
+int vt_abi_version(void);
+/* Use an existing CUDA stream (cudaStream_t, e.g. torch's current stream) instead of the context's own. */
+int vt_set_stream(vt_ctx *ctx, void *cuda_stream);
+int vt_sync(vt_ctx *ctx);
+
+/* ---- settings, materials, camera ----------------------------------------------------------------- */
+/* `data.settings` as read inside Camera.trace / Camera.tile (init.py:41-42, 53, 56, 85, 114, 131-141). */
+int vt_set_settings(vt_ctx *ctx, const vt_settings *host_settings);
+/* Material attribute bag (data.py:85-93) for ids 1..n; host_materials has n+1 rows. */
+int vt_set_materials(vt_ctx *ctx, const vt_material *host_materials, int n);
+/* cam.pos / cam.rot / cam.lens attribute writes (init.py:464-465, init.py:282). */
+int vt_set_camera(vt_ctx *ctx, const double pos[3], const double rot_xyzw[4], double lens);
+
+/* ---- world: what Camera.chunk_set / chunk_get expose (init.py:21-33) ------------------------------- */
+/* Declares the cell box covered by the camera's chunk dictionary: origin (world cell of the minimum corner)
+ * and dims (cells), both multiples of chunk_size.  Drops any previous world.  Needs vt_set_settings first. */
+int vt_set_world(vt_ctx *ctx, const int32_t origin[3], const int32_t dims[3]);
+/* Per-chunk-slot byte, [dims0/cs][dims1/cs][dims2/cs] (z fastest): 0 = no frame for that chunk (absent or
+ * culled, init.py:447-452), else Frame.resolution of the frame the camera holds (init.py:448-450). */
+int vt_set_chunk_table(vt_ctx *ctx, const uint8_t *host_res, int64_t n_slots);
+/* Upload m dirty bricks.  brick_coords[i] = brick index per axis relative to the world origin
+ * ((cell - origin) / 8); cells[i] = 512 material ids, index (lx*8 + ly)*8 + lz.  An all-zero brick releases
+ * its storage.  Stands in for chunk_set replacing one chunk's Frame (init.py:21-25, 450-452). */
+int vt_upload_bricks(vt_ctx *ctx, const int32_t *host_brick_coords, const uint8_t *host_cells, int m);
+/* Bulk path for synthetic / imported worlds: a dense [dims0][dims1][dims2] (z fastest) u8 array in DEVICE
+ * memory is bricked on the device; empty bricks get no storage. */
+int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells);
+/* Bytes of device memory held by bricks / number of non-empty bricks (reporting). */
+int vt_world_stats(vt_ctx *ctx, int64_t *n_bricks, int64_t *bytes);
+
+/* ---- render: Camera.tile (init.py:126-150) --------------------------------------------------------- */
+/* Pixel set of one call.  The reference hands each worker `settings.pixels[thread]` (data.py:70-77); here a
+ * call covers either a rectangle of interleaved row stripes or an explicit pixel list:
+ *   rect mode  (dev_pixels == NULL): pixels x0 <= x < x1, y0 <= y < y1 whose stripe (y / stripe_rows) %
+ *              stripe_count == stripe_index.  Output index i = row_local * (x1 - x0) + (x - x0), where
+ *              row_local counts the selected rows in increasing y (a compact band image).
+ *   list mode  (dev_pixels != NULL): n_pixels (x, y) int32 pairs; output index i = list position.       */
+typedef struct {
+    int32_t x0, y0, x1, y1;
+    int32_t stripe_rows, stripe_count, stripe_index;   /* 1, 1, 0 = every row */
+    int32_t reserved;
+    const int32_t *dev_pixels;
+    int64_t n_pixels;
+} vt_region;
+
+/* Outputs (device pointers; any may be NULL):
+ *   dev_rgba8    [n][4] u8: per-pixel mean of r, g, b and alpha = round(min(1, energy + shutter) * 255)
+ *                (init.py:141-146), truncated to u8 like a C cast
+ *   dev_mean     [n][4] f32: the same means before quantisation
+ *   dev_ray0     [n][VT_RAY_RECORD] f64, sample 0 of each pixel (parity probe): r, g, b, energy, bounces, step,
+ *                hits, first-hit x, y, z, first-hit flag, first-hit step, vel x, y, z, samples traced
+ *   dev_visited  u32 bitmask over chunk slots, OR-ed in (caller clears): ray.traversed (init.py:72-73, 143)
+ *   dev_counters [8] u64, added to (caller clears): rays, in-chunk samples, void samples, hits,
+ *                neighbour probes, chunk re-evaluations, loop iterations, 0
+ * frame_seed perturbs the Philox streams when settings.static is 0; ignored when it is 1. */
+int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
+              uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed);
+/* Number of output pixels a region produces (host arithmetic only). */
+int64_t vt_region_pixels(const vt_region *region);
+/* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */
+int64_t vt_launch_count(const vt_ctx *ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

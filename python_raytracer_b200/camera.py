@@ -1,0 +1,365 @@
+"""GpuCamera: the reference's ``Camera`` protocol (reference init.py:13-150) on top of libvoxtrace.so.
+
+Same attribute and method names as the reference class so ``Window``-style callers can swap it in:
+``pos``, ``rot``, ``lens``, ``chunks``, ``chunk_set``, ``chunk_get``, ``tile``.  The per-tile Python thread pool
+(init.py:162, 193-205) is replaced by one kernel launch per call; ``tile(thread, t)`` still returns
+``(rgba_bytes, traversed, thread)`` like init.py:149-150.
+
+No CPU fallback: constructing a GpuCamera without a CUDA device raises VoxtraceError.
+User-defined Python material callbacks cannot run inside a CUDA kernel and are rejected with a clear error
+(only ``lib.material`` / ``lib.material_background`` are compiled device functions).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import sys
+
+import numpy as np
+import torch
+
+from . import abi
+from .abi import VoxtraceError, VtMaterial, VtRegion
+from .settings import Settings
+from .world import WorldMirror, flatten_frame
+
+_UNSET = object()
+
+
+def _xyz(v):
+    if hasattr(v, "x"):
+        return float(v.x), float(v.y), float(v.z)
+    return float(v[0]), float(v[1]), float(v[2])
+
+
+def _xyzw(q):
+    if hasattr(q, "w"):
+        return float(q.x), float(q.y), float(q.z), float(q.w)
+    return float(q[0]), float(q[1]), float(q[2]), float(q[3])
+
+
+def _is_builtin(fn, name):
+    return callable(fn) and getattr(fn, "__name__", None) == name and getattr(fn, "__module__", None) == "lib"
+
+
+class GpuCamera:
+    def __init__(self, settings, device: int = 0, material_function=None, background_function=None,
+                 background=_UNSET):
+        """settings: reference ``data.settings`` store, dict or Settings.
+        material_function / background_function: the callables accepted as "the built-in" (pass ``lib.material``
+        and ``lib.material_background`` of the running engine); when omitted, functions named ``material`` /
+        ``material_background`` from a module called ``lib`` are accepted.
+        background: what ``data.background`` is set to (init.py:119): the built-in function or None."""
+        self._lib = abi.load()
+        if not torch.cuda.is_available():
+            raise VoxtraceError("GpuCamera needs a CUDA device; the GPU path has no CPU fallback")
+        self.settings = settings if isinstance(settings, Settings) else Settings.from_object(settings)
+        self._live_settings = None if isinstance(settings, (Settings, dict)) else settings
+        self.device = torch.device("cuda", device)
+        self._material_function = material_function
+        self._background_function = background_function
+        ctx = C.c_void_p()
+        if self._lib.vt_create(int(device), C.byref(ctx)) != 0:
+            raise VoxtraceError(self._lib.vt_last_error(None).decode())
+        self._ctx = ctx
+        # reference attributes (init.py:15-18)
+        self.pos = (0.0, 0.0, 0.0)
+        self.rot = (0.0, 0.0, 0.0, 0.0)
+        self.lens = float(self.settings.fov) * math.pi / 8
+        self.chunks = {}
+        self.background = background_function if background is _UNSET else background
+        # device-side state
+        self._mirror = None
+        self._uploaded = {}            # post -> (frame object, resolution) last flattened
+        self._mat_ids = {}             # id(Material) -> (index, Material)
+        self._dense_mode = False
+        self._settings_key = None
+        self._frame_seed = 0
+        self._visited = None
+        self._counters = torch.zeros(8, dtype=torch.int64, device=self.device)
+        self._pix_cache = {}
+        self._static_materials = None
+
+    # ------------------------------------------------------------------ plumbing
+    def _check(self, rc):
+        if rc != 0:
+            raise VoxtraceError(self._lib.vt_last_error(self._ctx).decode())
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            self._lib.vt_destroy(self._ctx)
+            self._ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.vt_launch_count(self._ctx))
+
+    def _push_settings(self):
+        if self._live_settings is not None:      # the engine mutates data.settings in place; re-read it
+            self.settings = Settings.from_object(self._live_settings)
+        if self.background is not None:
+            ok = (self.background is self._background_function) if self._background_function is not None \
+                else _is_builtin(self.background, "material_background")
+            if not ok:
+                raise VoxtraceError("custom background callbacks cannot run on the GPU path; use "
+                                    "lib.material_background or None (got %r)" % (self.background,))
+        key = (self.settings.key(), self.background is not None)
+        if key != self._settings_key:
+            st = self.settings.to_struct(background=self.background is not None)
+            self._check(self._lib.vt_set_settings(self._ctx, C.byref(st)))
+            self._settings_key = key
+
+    # ------------------------------------------------------------------ reference protocol: chunks
+    def chunk_set(self, post: tuple, chunk):
+        """init.py:21-25."""
+        if self._dense_mode:
+            raise VoxtraceError("chunk_set after set_world_dense: pick one world path per camera")
+        if chunk:
+            self.chunks[post] = chunk
+        elif post in self.chunks:
+            del self.chunks[post]
+
+    def chunk_get(self, pos):
+        """init.py:28-33."""
+        cs = self.settings.chunk_size
+        x, y, z = _xyz(pos)
+        post = ((x // cs) * cs, (y // cs) * cs, (z // cs) * cs)
+        return self.chunks.get(post)
+
+    def _material_id(self, mat):
+        ent = self._mat_ids.get(id(mat))
+        if ent is None:
+            fn = getattr(mat, "function", None)
+            ok = (fn is self._material_function) if self._material_function is not None else _is_builtin(fn, "material")
+            if not ok:
+                raise VoxtraceError(
+                    "material %r uses a custom Python function (%r); user-defined material callbacks cannot run "
+                    "on the GPU path -- only the built-in lib.material is compiled" % (mat, fn))
+            if len(self._mat_ids) >= 255:
+                raise VoxtraceError("more than 255 distinct materials")
+            ent = (len(self._mat_ids) + 1, mat)
+            self._mat_ids[id(mat)] = ent
+        return ent[0]
+
+    def _push_materials(self):
+        if self._static_materials is not None:
+            table = self._static_materials
+        else:
+            table = np.zeros((len(self._mat_ids) + 1, 7), np.float64)
+            for idx, m in self._mat_ids.values():
+                a = m.albedo
+                rgb = (a.r, a.g, a.b) if hasattr(a, "r") else tuple(a)
+                table[idx] = (rgb[0], rgb[1], rgb[2], m.roughness, m.absorption, m.ior, m.energy)
+        n = table.shape[0] - 1
+        arr = (VtMaterial * (n + 1))()
+        for i in range(n + 1):
+            arr[i].albedo[:] = [float(v) for v in table[i, :3]]
+            arr[i].roughness, arr[i].absorption, arr[i].ior, arr[i].energy = (float(v) for v in table[i, 3:7])
+        self._check(self._lib.vt_set_materials(self._ctx, arr, n))
+
+    def _sync_world(self):
+        """Flatten chunks whose Frame changed since the last call and upload the bricks they touch."""
+        if self._dense_mode:
+            return
+        cs = int(self.settings.chunk_size)
+        posts = [tuple(int(v) for v in p) for p in self.chunks]
+        if not posts:
+            posts = [(0, 0, 0)]
+        if self._mirror is None or self._mirror.cs != cs:
+            self._mirror, self._uploaded = WorldMirror(cs), {}
+        lo, dims = self._mirror.box_for(posts)
+        rebuilt = False
+        if not self._mirror.covers(lo, dims):
+            if self._mirror.origin is not None:      # grow: keep the old box inside the new one
+                old_lo, old_hi = self._mirror.origin, self._mirror.origin + np.array(self._mirror.cells.shape)
+                hi = np.maximum(lo + dims, old_hi)
+                lo = np.minimum(lo, old_lo)
+                dims = hi - lo
+            self._mirror.reset(lo, dims)
+            self._uploaded = {}
+            o = (C.c_int32 * 3)(*[int(v) for v in lo])
+            d = (C.c_int32 * 3)(*[int(v) for v in dims])
+            self._check(self._lib.vt_set_world(self._ctx, o, d))
+            rebuilt = True
+        dirty = set()
+        table_changed = rebuilt
+        for post in list(self._uploaded):
+            if post not in self.chunks:
+                dirty |= self._mirror.write_chunk(post, None, 0)
+                del self._uploaded[post]
+                table_changed = True
+        for post, frame in self.chunks.items():
+            key = tuple(int(v) for v in post)
+            prev = self._uploaded.get(key)
+            if prev is not None and prev[0] is frame and prev[1] == frame.resolution:
+                continue
+            cells = flatten_frame(frame, key, cs, self._material_id)
+            dirty |= self._mirror.write_chunk(key, cells, int(frame.resolution))
+            self._uploaded[key] = (frame, frame.resolution)
+            table_changed = True
+        if dirty:
+            coords, cells = self._mirror.gather_bricks(dirty)
+            self._check(self._lib.vt_upload_bricks(self._ctx, coords.ctypes.data, cells.ctypes.data, len(coords)))
+        if table_changed:
+            t = np.ascontiguousarray(self._mirror.chunk_res)
+            self._check(self._lib.vt_set_chunk_table(self._ctx, t.ctypes.data, t.size))
+            self._visited = None
+
+    def mark_dirty(self, post=None):
+        """Force re-flattening of one chunk (or all) after an in-place Frame edit."""
+        if post is None:
+            self._uploaded = {}
+        else:
+            self._uploaded.pop(tuple(int(v) for v in post), None)
+
+    # ------------------------------------------------------------------ bulk world path (synthetic / imported)
+    def set_world_dense(self, origin, cells, chunk_res, materials):
+        """Load a whole world at once: ``cells`` [nx, ny, nz] u8 material ids (numpy or CUDA tensor), world cell of
+        its corner ``origin`` (multiples of chunk_size), ``chunk_res`` [nx/cs, ny/cs, nz/cs] u8 (0 = no frame,
+        else Frame.resolution, what chunk_update would pick -- see lod_table) and the material table
+        [n+1, 7] = albedo r,g,b, roughness, absorption, ior, energy (row 0 unused)."""
+        self._push_settings()
+        self._dense_mode = True
+        self.chunks = {}
+        t = cells if isinstance(cells, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(cells, dtype=np.uint8))
+        t = t.to(self.device, dtype=torch.uint8).contiguous()
+        o = (C.c_int32 * 3)(*[int(v) for v in origin])
+        d = (C.c_int32 * 3)(*[int(v) for v in t.shape])
+        self._check(self._lib.vt_set_world(self._ctx, o, d))
+        torch.cuda.synchronize(self.device)
+        self._check(self._lib.vt_upload_dense(self._ctx, t.data_ptr()))
+        self._world_origin = np.asarray([int(v) for v in origin], np.int64)
+        self._world_shape = tuple(int(v) for v in t.shape)
+        self.set_chunk_res(chunk_res)
+        self._static_materials = np.ascontiguousarray(materials, dtype=np.float64)
+        assert self._static_materials.ndim == 2 and self._static_materials.shape[1] == 7
+
+    def set_chunk_res(self, chunk_res):
+        """Replace the per-chunk resolution table (LOD / culling state) of a dense world."""
+        cs = int(self.settings.chunk_size)
+        t = np.ascontiguousarray(chunk_res, dtype=np.uint8)
+        if tuple(t.shape) != tuple(v // cs for v in self._world_shape):
+            raise VoxtraceError("chunk_res shape %s does not match world %s / chunk_size %d" % (t.shape, self._world_shape, cs))
+        self._check(self._lib.vt_set_chunk_table(self._ctx, t.ctypes.data, t.size))
+        self._chunk_res_shape = t.shape
+        self._visited = None
+
+    def world_stats(self):
+        nb, by = C.c_int64(), C.c_int64()
+        self._check(self._lib.vt_world_stats(self._ctx, C.byref(nb), C.byref(by)))
+        return dict(bricks=nb.value, bytes=by.value)
+
+    # ------------------------------------------------------------------ render
+    def _chunk_grid(self):
+        if self._dense_mode:
+            return self._world_origin, self._chunk_res_shape
+        return self._mirror.origin, self._mirror.chunk_res.shape
+
+    def _prepare(self):
+        self._push_settings()
+        self._sync_world()
+        self._push_materials()
+        px, py, pz = _xyz(self.pos)
+        pos = (C.c_double * 3)(px, py, pz)
+        rot = (C.c_double * 4)(*_xyzw(self.rot))
+        self._check(self._lib.vt_set_camera(self._ctx, pos, rot, float(self.lens)))
+        self._check(self._lib.vt_set_stream(self._ctx, torch.cuda.current_stream(self.device).cuda_stream))
+        _, shape = self._chunk_grid()
+        nwords = (int(np.prod(shape)) + 31) // 32
+        if self._visited is None or self._visited.numel() != nwords:
+            self._visited = torch.zeros(nwords, dtype=torch.int32, device=self.device)
+
+    def render(self, pixels=None, rect=None, stripes=(1, 1, 0), want=("rgba8",), prepare=True, out=None,
+               clear=True):
+        """One pass of the hot path.  ``pixels``: [n,2] int32 (x,y) list (numpy / tensor) or None for the rectangle
+        ``rect`` = (x0, y0, x1, y1) (default: whole canvas) restricted to rows whose stripe
+        (y // stripes[0]) % stripes[1] == stripes[2].  ``want`` picks outputs among rgba8, mean, ray0, visited,
+        counters.  Returns a dict of CUDA tensors (nothing is copied to the host here)."""
+        if prepare:
+            self._prepare()
+        s = self.settings
+        reg = VtRegion()
+        reg.stripe_rows, reg.stripe_count, reg.stripe_index = (int(v) for v in stripes)
+        if pixels is not None:
+            p = pixels if isinstance(pixels, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(pixels, dtype=np.int32))
+            p = p.to(self.device, dtype=torch.int32).contiguous()
+            reg.dev_pixels, reg.n_pixels = p.data_ptr(), p.shape[0]
+            shape = (p.shape[0],)
+        else:
+            x0, y0, x1, y1 = rect if rect is not None else (0, 0, int(s.width), int(s.height))
+            reg.x0, reg.y0, reg.x1, reg.y1 = int(x0), int(y0), int(x1), int(y1)
+            reg.dev_pixels, reg.n_pixels = None, 0
+            n = int(self._lib.vt_region_pixels(C.byref(reg)))
+            shape = (n // max(1, x1 - x0), x1 - x0)
+        res = out if out is not None else {}
+        ptr = {}
+        for name, dt, tail in (("rgba8", torch.uint8, (4,)), ("mean", torch.float32, (4,)),
+                               ("ray0", torch.float64, (abi.RAY_RECORD,))):
+            if name in want:
+                if name not in res:
+                    res[name] = torch.empty(shape + tail, dtype=dt, device=self.device)
+                ptr[name] = res[name].data_ptr()
+        if clear:
+            self._visited.zero_()
+            self._counters.zero_()
+        self._check(self._lib.vt_render(self._ctx, C.byref(reg), ptr.get("rgba8"), ptr.get("mean"), ptr.get("ray0"),
+                                        self._visited.data_ptr() if "visited" in want else None,
+                                        self._counters.data_ptr() if "counters" in want else None,
+                                        int(self._frame_seed)))
+        if not s.static:
+            self._frame_seed += 1
+        if "visited" in want:
+            res["visited"] = self._visited
+        if "counters" in want:
+            res["counters"] = self._counters
+        return res
+
+    def visited_slots(self, visited_bits) -> np.ndarray:
+        """Bitmask -> u8 array over the chunk-slot grid."""
+        _, shape = self._chunk_grid()
+        words = visited_bits.cpu().numpy().view(np.uint32)
+        bits = np.unpackbits(words.view(np.uint8), bitorder="little")[:int(np.prod(shape))]
+        return bits.reshape(shape)
+
+    def traversed(self, visited_bits):
+        """Chunk-origin tuples of the slots a frame touched -- what tile() returns as ``traversed``
+        (init.py:143, 150); restricted to the chunk grid the camera holds, which is all init.py:447 looks up."""
+        origin, _ = self._chunk_grid()
+        cs = int(self.settings.chunk_size)
+        idx = np.argwhere(self.visited_slots(visited_bits))
+        return [tuple(int(v) for v in (i * cs + origin)) for i in idx]
+
+    # ------------------------------------------------------------------ reference protocol: tile
+    def _thread_pixels(self, thread, threads):
+        key = (thread, threads, int(self.settings.width), int(self.settings.height))
+        if key not in self._pix_cache:
+            w, h = key[2], key[3]
+            xs = torch.arange(w, dtype=torch.int32, device=self.device).view(-1, 1).expand(w, h)
+            ys = torch.arange(h, dtype=torch.int32, device=self.device).view(1, -1).expand(w, h)
+            sel = ((xs ^ ys) % threads) == thread               # data.py:76, x-major order like data.py:74-75
+            self._pix_cache = {key: torch.stack([xs[sel], ys[sel]], dim=1).contiguous()}
+        return self._pix_cache[key]
+
+    def tile(self, thread: int, t: int = 0):
+        """Camera.tile (init.py:126-150): returns (RGBA bytes of the full window, traversed, thread).  Pixels that
+        belong to other threads stay (0,0,0,0) like a fresh SRCALPHA surface.  With settings.threads == 1 the
+        whole frame is one launch."""
+        self._prepare()
+        s = self.settings
+        threads = max(1, int(getattr(s, "threads", 1) or 1))
+        if threads == 1:
+            out = self.render(want=("rgba8", "visited"), prepare=False)
+            frame = out["rgba8"]
+        else:
+            px = self._thread_pixels(int(thread), threads)
+            out = self.render(pixels=px, want=("rgba8", "visited"), prepare=False)
+            frame = torch.zeros((int(s.height), int(s.width), 4), dtype=torch.uint8, device=self.device)
+            frame[px[:, 1].long(), px[:, 0].long()] = out["rgba8"]
+        image = frame.cpu().numpy().tobytes()
+        return image, self.traversed(out["visited"]), thread

@@ -1,0 +1,542 @@
+// voxtrace.cu — C ABI (include/voxtrace.h) + kernels of the B200-native voxel ray-march path.
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false -shared -Xcompiler -fPIC
+// (see python_raytracer_b200/build.py).  No torch types cross this boundary.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "vt_device.cuh"
+
+using namespace vt;
+
+// ------------------------------------------------------------------------------------------------------
+// kernels
+
+// Camera.tile (reference init.py:126-150) for one pixel: per-pixel sample count, per-sample detail, trace,
+// alpha from energy, mean over samples, u8 quantisation.
+template <bool REC, bool FULL_TAIL>
+__device__ __forceinline__ void tile_pixel(const DevParams &P, long long i, int x, int y, Counters &c, unsigned &rays) {
+    const vt_settings &s = P.s;
+    double dir_x = -1.0 + ((double)x / (double)s.width) * 2.0;
+    double dir_y = -1.0 + ((double)y / (double)s.height) * 2.0;
+    double detail = 1.0 - fabs(dir_x * dir_y) * s.lod_edge;
+    int n = (int)rint((double)s.samples * detail);
+    if (n < 1) n = 1;
+    double sum_r = 0.0, sum_g = 0.0, sum_b = 0.0, sum_a = 0.0;
+    unsigned long long pix = (unsigned long long)y * (unsigned long long)s.width + (unsigned long long)x;
+    for (int sample = 0; sample < n; sample++) {
+        Rng g;
+        g.key0 = (uint32_t)pix; g.key1 = (uint32_t)(pix >> 32);
+        g.sample = (uint32_t)sample; g.seed_lo = P.seed_lo; g.seed_hi = P.seed_hi; g.draw = 0; g.w2 = g.w3 = 0;
+        double u = rng_next(g);                                           // drawn even when lod_random == 0 (init.py:139)
+        double ray_detail = detail / (1.0 + (double)sample * s.lod_samples) * (1.0 - s.lod_random * u);
+        Ray r;
+        trace<FULL_TAIL>(P, dir_x, dir_y, ray_detail, g, r, c, x, y);
+        rays++;
+        double alpha = rint(fmin(1.0, r.energy + s.shutter) * 255.0);    // init.py:141
+        sum_r += r.cr; sum_g += r.cg; sum_b += r.cb; sum_a += alpha;
+        if (REC && sample == 0) {
+            double *o = P.ray0 + (size_t)VT_RAY_RECORD * i;
+            o[0] = r.cr; o[1] = r.cg; o[2] = r.cb; o[3] = r.energy; o[4] = r.bounces; o[5] = r.step;
+            o[6] = (double)r.hits; o[7] = (double)r.fx; o[8] = (double)r.fy; o[9] = (double)r.fz;
+            o[10] = (double)r.fflag; o[11] = r.first_step; o[12] = r.vx; o[13] = r.vy; o[14] = r.vz; o[15] = (double)n;
+        }
+    }
+    double dn = (double)n;                                                // lib.average, lib.py:419-428
+    double mr = sum_r / dn, mg = sum_g / dn, mb = sum_b / dn, ma = sum_a / dn;
+    if (P.mean) {
+        float4 m4 = make_float4((float)mr, (float)mg, (float)mb, (float)ma);
+        reinterpret_cast<float4 *>(P.mean)[i] = m4;
+    }
+    if (P.rgba8) {
+        uchar4 q;
+        q.x = (unsigned char)fmin(255.0, mr); q.y = (unsigned char)fmin(255.0, mg);
+        q.z = (unsigned char)fmin(255.0, mb); q.w = (unsigned char)fmin(255.0, ma);
+        reinterpret_cast<uchar4 *>(P.rgba8)[i] = q;
+    }
+}
+
+struct RegionMap {
+    const int32_t *row_y;   // [band_rows] absolute y of each compact band row (rect mode)
+};
+
+template <bool REC, bool FULL_TAIL>
+__global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ DevParams P, const int32_t *__restrict__ row_y) {
+    Counters c = {0, 0, 0, 0, 0, 0};
+    unsigned rays = 0;
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const int bw = P.x1 - P.x0;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < P.n_pixels; i += stride) {
+        int x, y;
+        if (P.pixels) { x = __ldg(P.pixels + 2 * i); y = __ldg(P.pixels + 2 * i + 1); }
+        else { long long lr = i / bw; x = P.x0 + (int)(i - lr * bw); y = __ldg(row_y + lr); }
+        tile_pixel<REC, FULL_TAIL>(P, i, x, y, c, rays);
+    }
+    if (P.counters) {
+        unsigned v[7] = {rays, c.in_chunk, c.in_void, c.hits, c.probes, c.rechunk, c.iters};
+#pragma unroll
+        for (int k = 0; k < 7; k++) {
+            unsigned t = __reduce_add_sync(0xffffffffu, v[k]);
+            if ((threadIdx.x & 31) == 0 && t) atomicAdd(P.counters + k, (unsigned long long)t);
+        }
+    }
+}
+
+// scatter m staged bricks into their pool slots and patch the brick table
+__global__ void scatter_bricks_kernel(const uint8_t *__restrict__ staged, const uint32_t *__restrict__ slots,
+                                      const uint32_t *__restrict__ tab_index, const uint32_t *__restrict__ tab_value,
+                                      uint8_t *pool, uint32_t *brick_tab, int m) {
+    int b = blockIdx.x;
+    if (b >= m) return;
+    uint32_t slot = slots[b];
+    if (slot != 0xffffffffu) {
+        const uint4 *src = reinterpret_cast<const uint4 *>(staged + (size_t)b * 512);
+        uint4 *dst = reinterpret_cast<uint4 *>(pool + (size_t)slot * 512);
+        dst[threadIdx.x] = src[threadIdx.x];          // 32 threads x 16 B
+    }
+    if (threadIdx.x == 0) brick_tab[tab_index[b]] = tab_value[b];
+}
+
+// dense [nx][ny][nz] -> per-brick "has any solid cell" flag
+__global__ void brick_flags_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nbx, int nby, int nbz,
+                                   uint8_t *flags) {
+    long long nb = (long long)nbx * nby * nbz;
+    for (long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += (long long)gridDim.x * blockDim.x) {
+        int bz = (int)(b % nbz), by = (int)((b / nbz) % nby), bx = (int)(b / ((long long)nbz * nby));
+        unsigned any = 0;
+        for (int lx = 0; lx < 8 && !any; lx++)
+            for (int ly = 0; ly < 8 && !any; ly++) {
+                int x = bx * 8 + lx, y = by * 8 + ly;
+                if (x >= nx || y >= ny) continue;
+                for (int lz = 0; lz < 8; lz++) {
+                    int z = bz * 8 + lz;
+                    if (z < nz && dense[((size_t)x * ny + y) * nz + z]) { any = 1; break; }
+                }
+            }
+        flags[b] = (uint8_t)any;
+    }
+}
+
+// copy dense cells of every non-empty brick into its pool slot (one block of 512 threads per brick)
+__global__ void brick_fill_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nby, int nbz,
+                                  const uint32_t *__restrict__ brick_tab, long long nb, uint8_t *pool) {
+    for (long long b = blockIdx.x; b < nb; b += gridDim.x) {
+        uint32_t slot1 = brick_tab[b];
+        if (!slot1) continue;
+        int bz = (int)(b % nbz), by = (int)((b / nbz) % nby), bx = (int)(b / ((long long)nbz * nby));
+        int t = threadIdx.x, lx = t >> 6, ly = (t >> 3) & 7, lz = t & 7;
+        int x = bx * 8 + lx, y = by * 8 + ly, z = bz * 8 + lz;
+        uint8_t v = (x < nx && y < ny && z < nz) ? dense[((size_t)x * ny + y) * nz + z] : 0;
+        pool[(size_t)(slot1 - 1) * 512 + t] = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------------
+// host side: context + C ABI
+
+struct vt_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    std::string err;
+    long long launches = 0;
+
+    bool have_settings = false;
+    vt_settings s{};
+    int cs_shift = -1;
+
+    double cam_pos[3] = {0, 0, 0}, cam_rot[4] = {0, 0, 0, 0}, cam_lens = 0;
+    // lens tables (dof == 0): rebuilt when (lens, width, height, proportions) change
+    double *d_col_sc = nullptr, *d_row_sc = nullptr;
+    int tab_w = 0, tab_h = 0; double tab_lens = -1, tab_prop = -1;
+
+    // world
+    bool have_world = false;
+    int origin[3] = {0, 0, 0}, dims[3] = {0, 0, 0}, nb[3] = {0, 0, 0}, nc[3] = {0, 0, 0};
+    uint8_t *d_chunk_res = nullptr;
+    uint32_t *d_brick_tab = nullptr;
+    std::vector<uint32_t> h_brick_tab;          // host mirror: 0 = empty else slot + 1
+    uint8_t *d_pool = nullptr;
+    long long pool_cap = 0, pool_used = 0;      // in bricks
+    std::vector<uint32_t> free_slots;
+    double *d_mats = nullptr;                   // [256][8]
+
+    // region row map
+    int32_t *d_row_y = nullptr; int row_cap = 0;
+    std::vector<int32_t> h_row_y; int row_key[7] = {-1, -1, -1, -1, -1, -1, -1};
+};
+
+static std::string g_create_err;
+
+#define VT_CHECK(ctx, call)                                                                         \
+    do {                                                                                            \
+        cudaError_t e_ = (call);                                                                    \
+        if (e_ != cudaSuccess) {                                                                    \
+            (ctx)->err = std::string(#call) + ": " + cudaGetErrorString(e_);                        \
+            return 2;                                                                               \
+        }                                                                                           \
+    } while (0)
+
+static int fail(vt_ctx *ctx, const char *msg) { ctx->err = msg; return 1; }
+
+extern "C" int vt_abi_version(void) { return VT_ABI_VERSION; }
+
+extern "C" int vt_create(int device, vt_ctx **out) {
+    if (!out) { g_create_err = "vt_create: out is NULL"; return 1; }
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        g_create_err = std::string("vt_create: no usable CUDA device (") + cudaGetErrorString(e) + "); there is no CPU fallback";
+        return 2;
+    }
+    if (device < 0 || device >= n) { g_create_err = "vt_create: device ordinal out of range"; return 1; }
+    vt_ctx *ctx = new vt_ctx();
+    ctx->device = device;
+    if ((e = cudaSetDevice(device)) != cudaSuccess || (e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess ||
+        (e = cudaMalloc(&ctx->d_mats, 256 * 8 * sizeof(double))) != cudaSuccess ||
+        (e = cudaMemset(ctx->d_mats, 0, 256 * 8 * sizeof(double))) != cudaSuccess) {
+        g_create_err = std::string("vt_create: ") + cudaGetErrorString(e);
+        delete ctx;
+        return 2;
+    }
+    ctx->own_stream = true;
+    *out = ctx;
+    return 0;
+}
+
+static void free_world(vt_ctx *ctx) {
+    cudaFree(ctx->d_chunk_res); cudaFree(ctx->d_brick_tab); cudaFree(ctx->d_pool);
+    ctx->d_chunk_res = nullptr; ctx->d_brick_tab = nullptr; ctx->d_pool = nullptr;
+    ctx->pool_cap = ctx->pool_used = 0; ctx->free_slots.clear(); ctx->h_brick_tab.clear();
+    ctx->have_world = false;
+}
+
+extern "C" void vt_destroy(vt_ctx *ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    free_world(ctx);
+    cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+extern "C" const char *vt_last_error(const vt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+extern "C" int64_t vt_launch_count(const vt_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" int vt_set_stream(vt_ctx *ctx, void *cuda_stream) {
+    if (!ctx) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); ctx->own_stream = false; }
+    ctx->stream = (cudaStream_t)cuda_stream;
+    return 0;
+}
+
+extern "C" int vt_sync(vt_ctx *ctx) {
+    if (!ctx) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int vt_set_settings(vt_ctx *ctx, const vt_settings *hs) {
+    if (!ctx || !hs) return 1;
+    if (hs->width <= 0 || hs->height <= 0) return fail(ctx, "vt_set_settings: width/height must be positive");
+    if (hs->chunk_size <= 0 || hs->chunk_size > 4096) return fail(ctx, "vt_set_settings: chunk_size out of range");
+    if (hs->samples < 0) return fail(ctx, "vt_set_settings: samples must be >= 0");
+    if (!(hs->dist_max < 1e8) || !(hs->dist_min > -1e8)) return fail(ctx, "vt_set_settings: dist_min/dist_max out of range");
+    if (ctx->have_world && ctx->have_settings && hs->chunk_size != ctx->s.chunk_size)
+        return fail(ctx, "vt_set_settings: chunk_size changed while a world is loaded; call vt_set_world again");
+    ctx->s = *hs;
+    ctx->have_settings = true;
+    ctx->cs_shift = -1;
+    for (int k = 0; k < 13; k++) if ((1 << k) == hs->chunk_size) ctx->cs_shift = k;
+    return 0;
+}
+
+extern "C" int vt_set_materials(vt_ctx *ctx, const vt_material *hm, int n) {
+    if (!ctx || !hm) return 1;
+    if (n < 0 || n > VT_MAX_MATERIALS) return fail(ctx, "vt_set_materials: at most 255 materials (id 0 is empty)");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_mats, hm, (size_t)(n + 1) * sizeof(vt_material), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));   // host buffer may be reused on return
+    return 0;
+}
+
+extern "C" int vt_set_camera(vt_ctx *ctx, const double pos[3], const double rot[4], double lens) {
+    if (!ctx || !pos || !rot) return 1;
+    for (int a = 0; a < 3; a++)
+        if (!(fabs(pos[a]) < 1e9)) return fail(ctx, "vt_set_camera: position out of range (|p| < 1e9)");
+    memcpy(ctx->cam_pos, pos, sizeof ctx->cam_pos);
+    memcpy(ctx->cam_rot, rot, sizeof ctx->cam_rot);
+    ctx->cam_lens = lens;
+    return 0;
+}
+
+// ---- world ------------------------------------------------------------------------------------------
+extern "C" int vt_set_world(vt_ctx *ctx, const int32_t origin[3], const int32_t dims[3]) {
+    if (!ctx || !origin || !dims) return 1;
+    if (!ctx->have_settings) return fail(ctx, "vt_set_world: call vt_set_settings first (chunk_size)");
+    const int cs = ctx->s.chunk_size;
+    long long slots = 1, bricks = 1;
+    for (int a = 0; a < 3; a++) {
+        if (dims[a] <= 0 || dims[a] % cs != 0) return fail(ctx, "vt_set_world: dims must be positive multiples of chunk_size");
+        int r = origin[a] % cs;
+        if (r != 0) return fail(ctx, "vt_set_world: origin must be a multiple of chunk_size");
+        if (fabs((double)origin[a]) > 1e9 || dims[a] > (1 << 20)) return fail(ctx, "vt_set_world: box out of range");
+        slots *= dims[a] / cs; bricks *= (dims[a] + VT_BRICK - 1) / VT_BRICK;
+    }
+    if (bricks > (1LL << 31) || slots > (1LL << 31)) return fail(ctx, "vt_set_world: world too large");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    free_world(ctx);
+    for (int a = 0; a < 3; a++) {
+        ctx->origin[a] = origin[a]; ctx->dims[a] = dims[a];
+        ctx->nb[a] = (dims[a] + VT_BRICK - 1) / VT_BRICK; ctx->nc[a] = dims[a] / cs;
+    }
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_chunk_res, (size_t)slots));
+    VT_CHECK(ctx, cudaMemsetAsync(ctx->d_chunk_res, 0, (size_t)slots, ctx->stream));
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_brick_tab, (size_t)bricks * sizeof(uint32_t)));
+    VT_CHECK(ctx, cudaMemsetAsync(ctx->d_brick_tab, 0, (size_t)bricks * sizeof(uint32_t), ctx->stream));
+    ctx->h_brick_tab.assign((size_t)bricks, 0u);
+    ctx->have_world = true;
+    return 0;
+}
+
+extern "C" int vt_set_chunk_table(vt_ctx *ctx, const uint8_t *host_res, int64_t n_slots) {
+    if (!ctx || !host_res) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_set_chunk_table: no world (vt_set_world)");
+    long long slots = (long long)ctx->nc[0] * ctx->nc[1] * ctx->nc[2];
+    if (n_slots != slots) return fail(ctx, "vt_set_chunk_table: n_slots does not match the world's chunk grid");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_chunk_res, host_res, (size_t)slots, cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+static int grow_pool(vt_ctx *ctx, long long need) {
+    if (need <= ctx->pool_cap) return 0;
+    long long cap = ctx->pool_cap ? ctx->pool_cap : 1024;
+    while (cap < need) cap *= 2;
+    uint8_t *np = nullptr;
+    VT_CHECK(ctx, cudaMalloc(&np, (size_t)cap * 512));
+    if (ctx->d_pool && ctx->pool_used)
+        VT_CHECK(ctx, cudaMemcpyAsync(np, ctx->d_pool, (size_t)ctx->pool_used * 512, cudaMemcpyDeviceToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_pool);
+    ctx->d_pool = np; ctx->pool_cap = cap;
+    return 0;
+}
+
+extern "C" int vt_upload_bricks(vt_ctx *ctx, const int32_t *coords, const uint8_t *cells, int m) {
+    if (!ctx || (m > 0 && (!coords || !cells))) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_upload_bricks: no world (vt_set_world)");
+    if (m <= 0) return 0;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    std::vector<uint32_t> meta((size_t)m * 3);       // slots | table index | table value
+    uint32_t *slots = meta.data(), *tidx = slots + m, *tval = tidx + m;
+    long long need = ctx->pool_used;
+    for (int b = 0; b < m; b++) {
+        const int32_t *c = coords + 3 * b;
+        for (int a = 0; a < 3; a++)
+            if (c[a] < 0 || c[a] >= ctx->nb[a]) return fail(ctx, "vt_upload_bricks: brick coordinate outside the world");
+        uint32_t ti = (uint32_t)(((long long)c[0] * ctx->nb[1] + c[1]) * ctx->nb[2] + c[2]);
+        bool empty = true;
+        const uint64_t *q = reinterpret_cast<const uint64_t *>(cells + (size_t)b * 512);
+        uint64_t acc = 0;
+        if ((reinterpret_cast<uintptr_t>(q) & 7) == 0) { for (int k = 0; k < 64; k++) acc |= q[k]; empty = acc == 0; }
+        else { for (int k = 0; k < 512; k++) if (cells[(size_t)b * 512 + k]) { empty = false; break; } }
+        uint32_t cur = ctx->h_brick_tab[ti];
+        if (empty) {
+            if (cur) ctx->free_slots.push_back(cur - 1);
+            slots[b] = 0xffffffffu; tval[b] = 0;
+        } else {
+            uint32_t slot;
+            if (cur) slot = cur - 1;
+            else if (!ctx->free_slots.empty()) { slot = ctx->free_slots.back(); ctx->free_slots.pop_back(); }
+            else slot = (uint32_t)need++;
+            slots[b] = slot; tval[b] = slot + 1;
+        }
+        tidx[b] = ti;
+        ctx->h_brick_tab[ti] = tval[b];
+    }
+    if (int rc = grow_pool(ctx, need)) return rc;
+    ctx->pool_used = need;
+    uint8_t *d_stage = nullptr; uint32_t *d_meta = nullptr;
+    VT_CHECK(ctx, cudaMalloc(&d_stage, (size_t)m * 512));
+    VT_CHECK(ctx, cudaMalloc(&d_meta, meta.size() * sizeof(uint32_t)));
+    VT_CHECK(ctx, cudaMemcpyAsync(d_stage, cells, (size_t)m * 512, cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaMemcpyAsync(d_meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    scatter_bricks_kernel<<<m, 32, 0, ctx->stream>>>(d_stage, d_meta, d_meta + m, d_meta + 2 * m, ctx->d_pool, ctx->d_brick_tab, m);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_stage); cudaFree(d_meta);
+    return 0;
+}
+
+extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
+    if (!ctx || !dev_cells) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_upload_dense: no world (vt_set_world)");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const long long nb = (long long)ctx->nb[0] * ctx->nb[1] * ctx->nb[2];
+    uint8_t *d_flags = nullptr;
+    VT_CHECK(ctx, cudaMalloc(&d_flags, (size_t)nb));
+    int grid = (int)((nb + 127) / 128 < 148 * 32 ? (nb + 127) / 128 : 148 * 32);
+    brick_flags_kernel<<<grid, 128, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[0], ctx->nb[1], ctx->nb[2], d_flags);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    std::vector<uint8_t> flags((size_t)nb);
+    VT_CHECK(ctx, cudaMemcpyAsync(flags.data(), d_flags, (size_t)nb, cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_flags);
+    ctx->free_slots.clear();
+    long long used = 0;
+    for (long long b = 0; b < nb; b++) ctx->h_brick_tab[(size_t)b] = flags[(size_t)b] ? (uint32_t)(++used) : 0u;
+    ctx->pool_used = 0;                                  // nothing to preserve
+    if (int rc = grow_pool(ctx, used)) return rc;
+    ctx->pool_used = used;
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_brick_tab, ctx->h_brick_tab.data(), (size_t)nb * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    if (used) {
+        int g2 = (int)(nb < 148 * 64 ? nb : 148 * 64);
+        brick_fill_kernel<<<g2, 512, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], ctx->d_brick_tab, nb, ctx->d_pool);
+        ctx->launches++;
+        VT_CHECK(ctx, cudaGetLastError());
+    }
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int vt_world_stats(vt_ctx *ctx, int64_t *n_bricks, int64_t *bytes) {
+    if (!ctx) return 1;
+    long long live = ctx->pool_used - (long long)ctx->free_slots.size();
+    if (n_bricks) *n_bricks = live;
+    if (bytes) *bytes = ctx->pool_cap * 512 + (long long)ctx->h_brick_tab.size() * 4 + (long long)ctx->nc[0] * ctx->nc[1] * ctx->nc[2];
+    return 0;
+}
+
+// ---- render -----------------------------------------------------------------------------------------
+static bool row_selected(const vt_region *r, int y) {
+    int sr = r->stripe_rows > 0 ? r->stripe_rows : 1, sc = r->stripe_count > 0 ? r->stripe_count : 1;
+    return ((y / sr) % sc) == r->stripe_index;
+}
+
+extern "C" int64_t vt_region_pixels(const vt_region *r) {
+    if (!r) return 0;
+    if (r->dev_pixels) return r->n_pixels;
+    if (r->x1 <= r->x0 || r->y1 <= r->y0) return 0;
+    int64_t rows = 0;
+    for (int y = r->y0; y < r->y1; y++) rows += row_selected(r, y) ? 1 : 0;
+    return rows * (int64_t)(r->x1 - r->x0);
+}
+
+// Lens tables for dof == 0: the lens angles are separable (init.py:41-42: lens_x depends on the column only,
+// lens_y on the row only), so sin/cos of the half angles are evaluated once per column / row on the host with
+// the same libm the reference's interpreter calls (math.sin / math.cos, lib.py:327-332).
+static int update_lens_tables(vt_ctx *ctx) {
+    const vt_settings &s = ctx->s;
+    if (ctx->d_col_sc && ctx->tab_w == s.width && ctx->tab_h == s.height && ctx->tab_lens == ctx->cam_lens &&
+        ctx->tab_prop == s.proportions)
+        return 0;
+    cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); ctx->d_col_sc = ctx->d_row_sc = nullptr;
+    std::vector<double> col((size_t)s.width * 2), row((size_t)s.height * 2);
+    const double deg2rad = 3.14159265358979323846 / 180.0;
+    for (int x = 0; x < s.width; x++) {
+        double dir_x = -1.0 + ((double)x / (double)s.width) * 2.0;
+        double lens_x = (dir_x / s.proportions) * ctx->cam_lens;
+        double rad = (-lens_x) * deg2rad;
+        col[2 * x] = sin(rad / 2.0); col[2 * x + 1] = cos(rad / 2.0);
+    }
+    for (int y = 0; y < s.height; y++) {
+        double dir_y = -1.0 + ((double)y / (double)s.height) * 2.0;
+        double lens_y = (dir_y * s.proportions) * ctx->cam_lens;
+        double rad = (+lens_y) * deg2rad;
+        row[2 * y] = sin(rad / 2.0); row[2 * y + 1] = cos(rad / 2.0);
+    }
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_col_sc, col.size() * sizeof(double)));
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_row_sc, row.size() * sizeof(double)));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_col_sc, col.data(), col.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_row_sc, row.data(), row.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->tab_w = s.width; ctx->tab_h = s.height; ctx->tab_lens = ctx->cam_lens; ctx->tab_prop = s.proportions;
+    return 0;
+}
+
+static int update_row_map(vt_ctx *ctx, const vt_region *r, int *band_rows) {
+    int key[7] = {r->x0, r->y0, r->x1, r->y1, r->stripe_rows, r->stripe_count, r->stripe_index};
+    if (ctx->d_row_y && memcmp(key, ctx->row_key, sizeof key) == 0) { *band_rows = (int)ctx->h_row_y.size(); return 0; }
+    ctx->h_row_y.clear();
+    for (int y = r->y0; y < r->y1; y++) if (row_selected(r, y)) ctx->h_row_y.push_back(y);
+    int n = (int)ctx->h_row_y.size();
+    if (n > ctx->row_cap) {
+        cudaFree(ctx->d_row_y); ctx->d_row_y = nullptr;
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_row_y, (size_t)n * sizeof(int32_t)));
+        ctx->row_cap = n;
+    }
+    if (n) {
+        VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_row_y, ctx->h_row_y.data(), (size_t)n * sizeof(int32_t), cudaMemcpyHostToDevice, ctx->stream));
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    memcpy(ctx->row_key, key, sizeof key);
+    *band_rows = n;
+    return 0;
+}
+
+extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
+                         uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed) {
+    if (!ctx || !region) return 1;
+    if (!ctx->have_settings) return fail(ctx, "vt_render: no settings (vt_set_settings)");
+    if (!ctx->have_world) return fail(ctx, "vt_render: no world (vt_set_world)");
+    const vt_settings &s = ctx->s;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    DevParams P;
+    memset(&P, 0, sizeof P);
+    P.s = s;
+    P.cs_shift = ctx->cs_shift;
+    if (!s.static_noise) { P.seed_lo = (uint32_t)frame_seed; P.seed_hi = (uint32_t)(frame_seed >> 32); }
+    DevWorld &w = P.w;
+    w.ox = ctx->origin[0]; w.oy = ctx->origin[1]; w.oz = ctx->origin[2];
+    w.nx = ctx->dims[0]; w.ny = ctx->dims[1]; w.nz = ctx->dims[2];
+    w.nbx = ctx->nb[0]; w.nby = ctx->nb[1]; w.nbz = ctx->nb[2];
+    w.ncx = ctx->nc[0]; w.ncy = ctx->nc[1]; w.ncz = ctx->nc[2];
+    w.brick_tab = ctx->d_brick_tab; w.pool = ctx->d_pool; w.chunk_res = ctx->d_chunk_res; w.mats = ctx->d_mats;
+    memcpy(P.cam.pos, ctx->cam_pos, sizeof P.cam.pos);
+    memcpy(P.cam.rot, ctx->cam_rot, sizeof P.cam.rot);
+    P.cam.lens = ctx->cam_lens;
+    if (s.dof == 0.0) {
+        if (int rc = update_lens_tables(ctx)) return rc;
+        P.cam.col_sc = ctx->d_col_sc; P.cam.row_sc = ctx->d_row_sc;
+    }
+    if (region->dev_pixels) {
+        if (region->n_pixels < 0) return fail(ctx, "vt_render: negative n_pixels");
+        P.pixels = region->dev_pixels; P.n_pixels = region->n_pixels;
+    } else {
+        if (region->x0 < 0 || region->y0 < 0 || region->x1 > s.width || region->y1 > s.height || region->x1 < region->x0 ||
+            region->y1 < region->y0)
+            return fail(ctx, "vt_render: rectangle outside the canvas");
+        if (region->stripe_rows < 1 || region->stripe_count < 1 || region->stripe_index < 0 || region->stripe_index >= region->stripe_count)
+            return fail(ctx, "vt_render: bad stripe spec");
+        int band_rows = 0;
+        if (int rc = update_row_map(ctx, region, &band_rows)) return rc;
+        P.x0 = region->x0; P.y0 = region->y0; P.x1 = region->x1; P.y1 = region->y1;
+        P.stripe_rows = region->stripe_rows; P.stripe_count = region->stripe_count; P.stripe_index = region->stripe_index;
+        P.band_rows = band_rows;
+        P.n_pixels = (long long)band_rows * (region->x1 - region->x0);
+    }
+    if (P.n_pixels == 0) return 0;
+    P.rgba8 = dev_rgba8; P.mean = dev_mean; P.ray0 = dev_ray0; P.visited = dev_visited;
+    P.counters = reinterpret_cast<unsigned long long *>(dev_counters);
+    const int block = 128;
+    long long want = (P.n_pixels + block - 1) / block;
+    int grid = (int)(want < 148LL * 16 * 64 ? want : 148LL * 16 * 64);
+    if (dev_ray0) render_kernel<true, true><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
+    else render_kernel<false, false><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
