@@ -101,3 +101,32 @@ class WorldMirror:
             blk = self.cells[bx * 8:min(bx * 8 + 8, nx), by * 8:min(by * 8 + 8, ny), bz * 8:min(bz * 8 + 8, nz)]
             out[i, :blk.shape[0], :blk.shape[1], :blk.shape[2]] = blk
         return np.asarray(coords, dtype=np.int32).reshape(m, 3), out.reshape(m, 512)
+
+
+def lod_table(origin, present, cam_pos, chunk_size, chunk_lod, dist_max, visible=None):
+    """Per-chunk Frame.resolution as Window.chunk_update picks it (reference init.py:447-450):
+        pos = chunk origin + chunk_radius;  lod = min(trunc(dist(pos, cam) / (dist_max / (1 + chunk_lod))), chunk_lod)
+    and the camera receives the frame of resolution lod + 1.  ``present`` [ncx,ncy,ncz] marks chunks that hold
+    voxels; ``visible`` (optional, same shape) is the culling mask (`post_chunk in traversed`, init.py:447).
+    Returns u8 [ncx,ncy,ncz] with 0 for absent / culled chunks."""
+    present = np.asarray(present).astype(bool)
+    cs = int(chunk_size)
+    radius = round(cs / 2)
+    ix, iy, iz = np.meshgrid(*(np.arange(n) for n in present.shape), indexing="ij")
+    cx = ix * cs + int(origin[0]) + radius
+    cy = iy * cs + int(origin[1]) + radius
+    cz = iz * cs + int(origin[2]) + radius
+    d = np.sqrt((cx - float(cam_pos[0])) ** 2 + (cy - float(cam_pos[1])) ** 2 + (cz - float(cam_pos[2])) ** 2)
+    lod = np.minimum(np.trunc(d / (dist_max / (1 + chunk_lod))), chunk_lod).astype(np.uint8)
+    res = np.where(present, lod + 1, 0).astype(np.uint8)
+    if visible is not None:
+        res = np.where(np.asarray(visible).astype(bool), res, 0).astype(np.uint8)
+    return res
+
+
+def chunk_presence(cells, chunk_size):
+    """[nx,ny,nz] cells -> bool [ncx,ncy,ncz]: chunk holds at least one voxel (init.py:440-446)."""
+    cs = int(chunk_size)
+    nx, ny, nz = cells.shape
+    v = np.asarray(cells).reshape(nx // cs, cs, ny // cs, cs, nz // cs, cs)
+    return v.any(axis=(1, 3, 5))

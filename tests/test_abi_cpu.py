@@ -95,3 +95,17 @@ def test_flatten_frame_precedence_and_lod():
     out = flatten_frame(g, (-16, 0, -16), 16, ids.__getitem__)
     assert out[1, 0, 13] == 1
     assert out[4, 3, 1] == 2 and out[7, 6, 4] == 2 and (out == 2).sum() == 8 and (out > 0).sum() == 9
+
+
+def test_lod_table_matches_reference_chunk_update():
+    """The LOD the reference's own chunk_update chose (stored in every golden case) is reproduced by lod_table."""
+    from python_raytracer_b200.world import chunk_presence, lod_table
+    from tests.golden_util import case_names, load_case
+    for name in case_names():
+        c = load_case(name)
+        s = c["settings"]
+        if s["culling"]:
+            continue
+        present = chunk_presence(c["cells"], s["chunk_size"])
+        res = lod_table(c["origin"], present, c["cam_pos"], s["chunk_size"], s["chunk_lod"], s["dist_max"])
+        assert np.array_equal(res, c["chunk_res"]), name

@@ -40,14 +40,15 @@ def test_rng_free_matches_reference(name):
     c = load_case(name)
     g = gpu_case(c)
     ref = c["ray0"]
-    # first-hit voxel + flag + step at which it happened: bit-exact
-    assert np.array_equal(g["ray0"][:, 7:12], ref[:, 7:12])
+    # first-hit voxel index + flag: bit-exact
+    assert np.array_equal(g["ray0"][:, 7:11], ref[:, 7:11])
     assert np.array_equal(g["ray0"][:, 6], ref[:, 6])                      # number of material interactions
     # colour: integers 0..255; report flips explicitly instead of hiding them in a tolerance
     flips = int((g["ray0"][:, 0:3] != ref[:, 0:3]).any(axis=1).sum())
     assert flips == 0, "%d pixels differ in 8-bit colour" % flips
     assert np.abs(g["mean"] - c["mean"]).max() <= 1e-4
-    np.testing.assert_allclose(g["ray0"][:, [3, 4, 5, 12, 13, 14]], ref[:, [3, 4, 5, 12, 13, 14]], rtol=1e-12, atol=1e-12)
+    # fp64 state: device pow / sincos differ from libm in the last ulp (DESIGN.md "numerics"); nothing more
+    np.testing.assert_allclose(g["ray0"][:, [3, 4, 5, 11, 12, 13, 14]], ref[:, [3, 4, 5, 11, 12, 13, 14]], rtol=1e-11, atol=1e-11)
     assert np.array_equal(g["ray0"][:, 15], c["nsamp"])
     assert np.array_equal(g["visited"], c["visited"])
     assert np.array_equal(g["rgba8"], np.trunc(c["mean"]).astype(np.uint8))
@@ -64,11 +65,11 @@ def test_matches_oracle_same_streams(name):
     o = cport.render(c["settings"], c["cam_pos"], c["cam_rot"], float(c["cam_lens"]), world, pixels=c["pixels"],
                      rng=cport.RNG_PHILOX, seed=0)
     n = len(c["pixels"])
-    bad = (g["ray0"][:, [0, 1, 2, 6, 7, 8, 9, 10, 11]] != o["ray0"][:, [0, 1, 2, 6, 7, 8, 9, 10, 11]]).any(axis=1)
+    bad = (g["ray0"][:, [0, 1, 2, 6, 7, 8, 9, 10]] != o["ray0"][:, [0, 1, 2, 6, 7, 8, 9, 10]]).any(axis=1)
     # a 1-ulp difference in a jittered direction can move a sample across a cell face; allow a handful, count them
     assert bad.sum() <= max(0, int(2e-4 * n)) if stochastic(c) else bad.sum() == 0, "%d / %d rays differ" % (bad.sum(), n)
     ok = ~bad
-    np.testing.assert_allclose(g["ray0"][ok][:, [3, 4, 5, 12, 13, 14]], o["ray0"][ok][:, [3, 4, 5, 12, 13, 14]], rtol=1e-9, atol=1e-9)
+    np.testing.assert_allclose(g["ray0"][ok][:, [3, 4, 5, 11, 12, 13, 14]], o["ray0"][ok][:, [3, 4, 5, 11, 12, 13, 14]], rtol=1e-9, atol=1e-9)
     assert np.array_equal(g["ray0"][:, 15], o["nsamp"])
     pix_bad = np.abs(g["mean"] - o["mean"]).max(axis=1) > 1e-4
     assert pix_bad.sum() <= bad.sum() * 1 + (int(2e-4 * n * 5) if stochastic(c) else 0)
