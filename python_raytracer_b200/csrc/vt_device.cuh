@@ -45,6 +45,9 @@ struct DevParams {
     int x0, y0, x1, y1, stripe_rows, stripe_count, stripe_index, band_rows;
     const int32_t *pixels;
     long long n_pixels;
+    // warp tiling: `group` lanes per pixel, 32/group pixels per warp arranged tile_w x tile_h
+    int group, group_shift, tile_w, tile_w_shift, tile_h, tiles_x;
+    long long n_warps;
     // outputs
     uint8_t *rgba8;
     float *mean;
@@ -219,73 +222,131 @@ __device__ __forceinline__ void mark_visited(uint32_t *visited, int slot) {
     if (!(*(volatile uint32_t *)word & bit)) atomicOr(word, bit);
 }
 
-// Camera.trace (init.py:37-121).  FULL_TAIL = false lets a ray stop once it is outside the world box and
-// moving away from it on that axis: nothing it could still touch changes colour, energy, first hit or the
-// visited set of existing chunks (only ray.step / ray.pos, which no caller of tile() sees).
+// Brick-table entry cache: consecutive samples of a ray mostly stay inside one 8^3 brick, so the table is
+// re-read only when the brick coordinate changes (one dependent load per sample instead of two).
+struct BrickCache {
+    int key;            // packed brick coordinate, -1 = nothing cached
+    uint32_t slot1;     // table entry: 0 = empty brick, else pool slot + 1
+};
+
+__device__ __forceinline__ int get_voxel_cached(const DevWorld &w, int cs, int cx, int cy, int cz, int res, int px,
+                                                int py, int pz, BrickCache &bc) {
+    int qx = px, qy = py, qz = pz;
+    if (res > 1) { qx = ifloordiv(px, res) * res; qy = ifloordiv(py, res) * res; qz = ifloordiv(pz, res) * res; }
+    if (qx < cx || qy < cy || qz < cz || qx >= cx + cs || qy >= cy + cs || qz >= cz + cs) return 0;
+    int rx = qx - w.ox, ry = qy - w.oy, rz = qz - w.oz;
+    int key = ((rx >> 3) * w.nby + (ry >> 3)) * w.nbz + (rz >> 3);
+    if (key != bc.key) { bc.key = key; bc.slot1 = __ldg(&w.brick_tab[key]); }
+    if (bc.slot1 == 0u) return 0;
+    return __ldg(&w.pool[(size_t)(bc.slot1 - 1u) * 512u + (((rx & 7) << 6) | ((ry & 7) << 3) | (rz & 7))]);
+}
+
+// void step of init.py:114: 1 + |radius - (min(pos) + radius) % chunk_size| with Python's float modulo.
+// For a power-of-two chunk size a/cs, floor and cs*k are exact, so a - cs*floor(a/cs) is the same single rounding
+// Python performs (fmod is exact, then `mod += cs` rounds once for negatives); otherwise use fmod itself.
+__device__ __forceinline__ double void_step(double px, double py, double pz, int radius, int cs, int cs_shift) {
+    double a = fmin(px, fmin(py, pz)) + (double)radius;
+    double m;
+    if (cs_shift >= 0) { double dcs = (double)cs; m = a - dcs * floor(a / dcs); }
+    else m = py_mod_pos(a, (double)cs);
+    return 1.0 + fabs((double)radius - m);
+}
+
+// Camera.trace (init.py:37-121), executed by a whole warp in lock step: every lane owns one ray.
+//
+// The reference's loop body mixes a cheap common case (advance one sample) with a rare expensive one (a material
+// hit: pow, divisions, three neighbour probes, RNG).  Run naively, the lanes of a warp serialise on the rare
+// branch.  Here each round has two phases: (1) every live lane marches until it finds a solid cell or dies;
+// (2) the lanes that found one shade together.  Sample positions and their order per ray are unchanged.
+//
+// FULL_TAIL = false lets a ray stop once it is outside the world box and moving away from it on that axis:
+// nothing it could still touch changes colour, energy, first hit or the visited set of existing chunks (only
+// ray.step / ray.pos, which no caller of tile() sees).
 template <bool FULL_TAIL>
-__device__ __forceinline__ void trace(const DevParams &P, double dir_x, double dir_y, double detail, Rng &g, Ray &r,
-                                      Counters &c, int px_x, int px_y) {
+__device__ __forceinline__ void trace_warp(const DevParams &P, bool valid, double dir_x, double dir_y, double detail,
+                                           Rng &g, Ray &r, Counters &c, int px_x, int px_y) {
     const vt_settings &s = P.s;
     const DevWorld &w = P.w;
     const int cs = s.chunk_size, cs_shift = P.cs_shift;
-    double sy, cy, sz, cz;
-    if (s.dof == 0.0 && P.cam.col_sc) {
-        sy = __ldg(P.cam.col_sc + 2 * px_x); cy = __ldg(P.cam.col_sc + 2 * px_x + 1);
-        sz = __ldg(P.cam.row_sc + 2 * px_y); cz = __ldg(P.cam.row_sc + 2 * px_y + 1);
-    } else {
-        const double deg2rad = 3.14159265358979323846 / 180.0;
-        double lens_x = (dir_x / s.proportions) * P.cam.lens + rng_rand(g, s.dof);
-        double lens_y = (dir_y * s.proportions) * P.cam.lens + rng_rand(g, s.dof);
-        double rad_y = (-lens_x) * deg2rad, rad_z = (+lens_y) * deg2rad;
-        sincos(rad_y / 2.0, &sy, &cy);
-        sincos(rad_z / 2.0, &sz, &cz);
-    }
-    double dx, dy, dz;
-    ray_dir(P.cam, sy, cy, sz, cz, dx, dy, dz);
-
-    r.cr = r.cg = r.cb = 0.0; r.energy = 0.0; r.step = 0.0; r.bounces = 0.0;
-    r.px = P.cam.pos[0] + dx * s.dist_min; r.py = P.cam.pos[1] + dy * s.dist_min; r.pz = P.cam.pos[2] + dz * s.dist_min;
-    r.vx = dx; r.vy = dy; r.vz = dz;
-    r.life = (s.dist_max - s.dist_min) * detail;
+    r.cr = r.cg = r.cb = 0.0; r.energy = 0.0; r.step = 0.0; r.bounces = 0.0; r.life = 0.0;
+    r.px = r.py = r.pz = 0.0; r.vx = r.vy = r.vz = 0.0;
     r.hits = 0; r.fflag = 0; r.fx = r.fy = r.fz = 0; r.first_step = -1.0;
-
-    int cx = 0, cy_ = 0, cz_ = 0;        // chunk_min; chunk_max = chunk_min + cs except for the initial (0,0,0)/(0,0,0)
-    int hx = 0, hy = 0, hz = 0;          // chunk_max
-    int res = 0;                         // 0 == `chunk is None`
-    const int wx1 = w.ox + w.nx, wy1 = w.oy + w.ny, wz1 = w.oz + w.nz;
-
-    while (r.step < r.life) {
-        c.iters++;
-        int ix = __double2int_rd(r.px), iy = __double2int_rd(r.py), iz = __double2int_rd(r.pz);
-        if (!(axis_inside(r.px, ix, cx, hx) && axis_inside(r.py, iy, cy_, hy) && axis_inside(r.pz, iz, cz_, hz))) {
-            // init.py:67-73
-            cx = snap_chunk(ix, cs, cs_shift); cy_ = snap_chunk(iy, cs, cs_shift); cz_ = snap_chunk(iz, cs, cs_shift);
-            hx = cx + cs; hy = cy_ + cs; hz = cz_ + cs;
-            int slot = chunk_slot(w, cs, cs_shift, cx, cy_, cz_);
-            res = 0;
-            if (slot >= 0) { res = __ldg(&w.chunk_res[slot]); mark_visited(P.visited, slot); }
-            c.rechunk++;
-            if (!FULL_TAIL && slot < 0) {
-                bool gone = (ix >= wx1 && r.vx >= 0.0) || (ix < w.ox && r.vx <= 0.0) ||
-                            (iy >= wy1 && r.vy >= 0.0) || (iy < w.oy && r.vy <= 0.0) ||
-                            (iz >= wz1 && r.vz >= 0.0) || (iz < w.oz && r.vz <= 0.0);
-                if (gone) break;
-            }
+    if (valid) {
+        double sy, cy, sz, cz;
+        if (s.dof == 0.0 && P.cam.col_sc) {
+            sy = __ldg(P.cam.col_sc + 2 * px_x); cy = __ldg(P.cam.col_sc + 2 * px_x + 1);
+            sz = __ldg(P.cam.row_sc + 2 * px_y); cz = __ldg(P.cam.row_sc + 2 * px_y + 1);
+        } else {
+            const double deg2rad = 3.14159265358979323846 / 180.0;
+            double lens_x = (dir_x / s.proportions) * P.cam.lens + rng_rand(g, s.dof);
+            double lens_y = (dir_y * s.proportions) * P.cam.lens + rng_rand(g, s.dof);
+            double rad_y = (-lens_x) * deg2rad, rad_z = (+lens_y) * deg2rad;
+            sincos(rad_y / 2.0, &sy, &cy);
+            sincos(rad_z / 2.0, &sz, &cz);
         }
-        double step;
-        if (res) {
-            c.in_chunk++;
-            int id = get_voxel(w, cs, cx, cy_, cz_, res, ix, iy, iz);
-            if (id) {
-                const double *m = w.mats + 8 * id;
-                if (!r.fflag) { r.fflag = 1; r.fx = ix; r.fy = iy; r.fz = iz; r.first_step = r.step; }
-                r.hits++; c.hits++;
-                double bounce = shade_material(r, m, s, g);                       // init.py:81
-                r.bounces += bounce;
-                r.life /= (double)res + bounce * s.lod_bounces;                   // init.py:83
-                double ref = fmax(fabs(r.vx), fmax(fabs(r.vy), fabs(r.vz)));     // vec3.normalize, lib.py:310-314
-                if (ref != 0.0 && ref != 1.0) { r.vx /= ref; r.vy /= ref; r.vz /= ref; }
-                if (r.step >= r.life || r.energy >= s.max_light || r.bounces >= s.max_bounces + 1.0) break;
+        double dx, dy, dz;
+        ray_dir(P.cam, sy, cy, sz, cz, dx, dy, dz);
+        r.px = P.cam.pos[0] + dx * s.dist_min; r.py = P.cam.pos[1] + dy * s.dist_min; r.pz = P.cam.pos[2] + dz * s.dist_min;
+        r.vx = dx; r.vy = dy; r.vz = dz;
+        r.life = (s.dist_max - s.dist_min) * detail;
+    }
+
+    int cx = 0, cy_ = 0, cz_ = 0;        // chunk_min
+    int hx = 0, hy = 0, hz = 0;          // chunk_max (= chunk_min + cs except for the initial (0,0,0)/(0,0,0))
+    int res = 0;                         // 0 == `chunk is None`
+    int ix = 0, iy = 0, iz = 0;          // floor(pos) of the sample being examined
+    int hit = 0;                         // material id found by phase 1, consumed by phase 2
+    BrickCache bc; bc.key = -1; bc.slot1 = 0u;
+    const int wx1 = w.ox + w.nx, wy1 = w.oy + w.ny, wz1 = w.oz + w.nz;
+    bool alive = valid && (r.step < r.life);
+
+    for (;;) {
+        // ---- phase 1: march to the next solid cell (init.py:66-77, 114-116) -------------------------------
+        while (alive && !hit) {
+            c.iters++;
+            ix = __double2int_rd(r.px); iy = __double2int_rd(r.py); iz = __double2int_rd(r.pz);
+            if (!(axis_inside(r.px, ix, cx, hx) && axis_inside(r.py, iy, cy_, hy) && axis_inside(r.pz, iz, cz_, hz))) {
+                cx = snap_chunk(ix, cs, cs_shift); cy_ = snap_chunk(iy, cs, cs_shift); cz_ = snap_chunk(iz, cs, cs_shift);
+                hx = cx + cs; hy = cy_ + cs; hz = cz_ + cs;
+                int slot = chunk_slot(w, cs, cs_shift, cx, cy_, cz_);
+                res = 0;
+                if (slot >= 0) { res = __ldg(&w.chunk_res[slot]); mark_visited(P.visited, slot); }
+                c.rechunk++;
+                if (!FULL_TAIL && slot < 0) {
+                    bool gone = (ix >= wx1 && r.vx >= 0.0) || (ix < w.ox && r.vx <= 0.0) ||
+                                (iy >= wy1 && r.vy >= 0.0) || (iy < w.oy && r.vy <= 0.0) ||
+                                (iz >= wz1 && r.vz >= 0.0) || (iz < w.oz && r.vz <= 0.0);
+                    if (gone) { alive = false; break; }
+                }
+            }
+            double step;
+            if (res) {
+                c.in_chunk++;
+                hit = get_voxel_cached(w, cs, cx, cy_, cz_, res, ix, iy, iz, bc);
+                if (hit) break;                       // shade in phase 2, then advance there
+                step = (double)res;
+            } else {
+                c.in_void++;
+                step = void_step(r.px, r.py, r.pz, s.chunk_radius, cs, cs_shift);
+            }
+            r.step += step;
+            r.px += r.vx * step; r.py += r.vy * step; r.pz += r.vz * step;
+            alive = r.step < r.life;
+        }
+        if (!__any_sync(0xffffffffu, hit != 0)) break;
+        // ---- phase 2: material interaction (init.py:78-111), all hitting lanes together ----------------------
+        if (hit) {
+            const double *m = w.mats + 8 * hit;
+            if (!r.fflag) { r.fflag = 1; r.fx = ix; r.fy = iy; r.fz = iz; r.first_step = r.step; }
+            r.hits++; c.hits++;
+            double bounce = shade_material(r, m, s, g);                           // init.py:81
+            r.bounces += bounce;
+            r.life /= (double)res + bounce * s.lod_bounces;                       // init.py:83
+            double ref = fmax(fabs(r.vx), fmax(fabs(r.vy), fabs(r.vz)));         // vec3.normalize, lib.py:310-314
+            if (ref != 0.0 && ref != 1.0) { r.vx /= ref; r.vy /= ref; r.vz /= ref; }
+            if (r.step >= r.life || r.energy >= s.max_light || r.bounces >= s.max_bounces + 1.0) {
+                alive = false;                                                    // `break`, init.py:85-86
+            } else {
                 double ior = __ldg(m + 5);
                 if (ior != 0.0) {                                                 // init.py:92-111
                     double direction = (ior - 0.5) * 2.0;
@@ -293,21 +354,19 @@ __device__ __forceinline__ void trace(const DevParams &P, double dir_x, double d
 #pragma unroll
                     for (int a = 0; a < 3; a++) {
                         double va = a == 0 ? r.vx : a == 1 ? r.vy : r.vz;
-                        double qx = r.px, qy = r.py, qz = r.pz;
-                        double &qa = a == 0 ? qx : a == 1 ? qy : qz;
+                        double qa = a == 0 ? r.px : a == 1 ? r.py : r.pz;
                         qa = (va < direction) ? qa + 1.0 : qa - 1.0;
-                        int jx = ix, jy = iy, jz = iz;
-                        int &ja = a == 0 ? jx : a == 1 ? jy : jz;
-                        ja = __double2int_rd(qa);
+                        int ja = __double2int_rd(qa);
+                        int jx = a == 0 ? ja : ix, jy = a == 1 ? ja : iy, jz = a == 2 ? ja : iz;
                         int lo = a == 0 ? cx : a == 1 ? cy_ : cz_, hi = a == 0 ? hx : a == 1 ? hy : hz;
                         int nid = 0;
                         if (axis_inside(qa, ja, lo, hi)) {
-                            nid = get_voxel(w, cs, cx, cy_, cz_, res, jx, jy, jz); c.probes++;
+                            nid = get_voxel_cached(w, cs, cx, cy_, cz_, res, jx, jy, jz, bc); c.probes++;
                         } else {                                                  // Camera.chunk_get, init.py:28-33
                             int nx = snap_chunk(jx, cs, cs_shift), ny = snap_chunk(jy, cs, cs_shift), nz = snap_chunk(jz, cs, cs_shift);
                             int nslot = chunk_slot(w, cs, cs_shift, nx, ny, nz);
                             int nres = nslot >= 0 ? (int)__ldg(&w.chunk_res[nslot]) : 0;
-                            if (nres) { nid = get_voxel(w, cs, nx, ny, nz, nres, jx, jy, jz); c.probes++; }
+                            if (nres) { nid = get_voxel_cached(w, cs, nx, ny, nz, nres, jx, jy, jz, bc); c.probes++; }
                         }
                         flip[a] = (nid == 0) || (__ldg(w.mats + 8 * nid + 5) != ior);
                     }
@@ -315,18 +374,15 @@ __device__ __forceinline__ void trace(const DevParams &P, double dir_x, double d
                     if (flip[1]) r.vy -= r.vy * ior * 2.0;
                     if (flip[2]) r.vz -= r.vz * ior * 2.0;
                 }
+                double step = (double)res;                                        // init.py:114-116
+                r.step += step;
+                r.px += r.vx * step; r.py += r.vy * step; r.pz += r.vz * step;
+                alive = r.step < r.life;
             }
-            step = (double)res;
-        } else {
-            c.in_void++;
-            double mn = fmin(r.px, fmin(r.py, r.pz));
-            step = 1.0 + fabs((double)s.chunk_radius - py_mod_pos(mn + (double)s.chunk_radius, (double)cs));
+            hit = 0;
         }
-        // init.py:114-116
-        r.step += step;
-        r.px += r.vx * step; r.py += r.vy * step; r.pz += r.vz * step;
     }
-    if (s.background) shade_background(r, s);                                     // init.py:119-120
+    if (valid && s.background) shade_background(r, s);                             // init.py:119-120
 }
 
 }  // namespace vt
