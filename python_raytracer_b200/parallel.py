@@ -22,32 +22,26 @@ def stripe_rows(height: int, rank: int, world: int, stripe: int = STRIPE_ROWS) -
     return y[(y // stripe) % world == rank]
 
 
-class FrameRenderer:
-    """Per-rank band buffers + the gather to rank 0."""
+class StripeGather:
+    """Band buffers and the collective that assembles them; device-agnostic (CUDA + NCCL, or CPU + gloo in tests)."""
 
-    def __init__(self, cam, rank: int, world: int, stripe: int = STRIPE_ROWS):
-        self.cam, self.rank, self.world, self.stripe = cam, rank, world, stripe
-        s = cam.settings
-        self.w, self.h = int(s.width), int(s.height)
+    def __init__(self, width, height, rank, world, device, stripe=STRIPE_ROWS):
+        self.w, self.h, self.rank, self.world, self.stripe, self.device = int(width), int(height), rank, world, stripe, device
         self.rows = [stripe_rows(self.h, r, world, stripe) for r in range(world)]
         self.max_rows = max(len(r) for r in self.rows)
-        dev = cam.device
-        # padded so every rank contributes the same byte count to the gather
-        self.frame = torch.zeros((self.h, self.w, 4), dtype=torch.uint8, device=dev) if rank == 0 else None
-        # one GPU: the band IS the frame
-        self.band = self.frame if world == 1 else torch.zeros((self.max_rows, self.w, 4), dtype=torch.uint8, device=dev)
         self.my_rows = len(self.rows[rank])
+        self.frame = torch.zeros((self.h, self.w, 4), dtype=torch.uint8, device=device) if rank == 0 else None
+        # one GPU: the band IS the frame; otherwise bands are padded to a common size for the gather
+        self.band = self.frame if world == 1 else torch.zeros((self.max_rows, self.w, 4), dtype=torch.uint8, device=device)
         if world > 1 and rank == 0:
             self.recv = [torch.empty_like(self.band) for _ in range(world)]
-            self.row_idx = [torch.from_numpy(r).to(dev) for r in self.rows]
+            self.row_idx = [torch.from_numpy(r).to(device) for r in self.rows]
 
-    def render(self, prepare=True, want=("rgba8",)):
-        """Render this rank's stripes into its band (one kernel launch)."""
-        out = {"rgba8": self.band[:self.my_rows]}
-        return self.cam.render(stripes=(self.stripe, self.world, self.rank), want=want, prepare=prepare, out=out)
+    def my_band(self):
+        return self.band[:self.my_rows]
 
     def gather(self):
-        """Bands -> full frame on rank 0 (returns it there, None elsewhere)."""
+        """Bands -> full frame on rank 0 (returned there, None elsewhere)."""
         if self.world == 1:
             return self.frame
         dist.gather(self.band, self.recv if self.rank == 0 else None, dst=0)
@@ -58,15 +52,28 @@ class FrameRenderer:
         return None
 
     def reduce_visited(self, visited_bits):
-        """OR of the per-rank visited-chunk bitmasks on every rank."""
+        """OR of the per-rank visited-chunk bitmasks (int32 words), on every rank."""
         if self.world == 1:
             return visited_bits
         bits = visited_bits.view(torch.uint8)
-        expanded = ((bits.unsqueeze(1) >> torch.arange(8, device=bits.device, dtype=torch.uint8)) & 1).contiguous()
-        dist.all_reduce(expanded, op=dist.ReduceOp.MAX)
-        weights = (1 << torch.arange(8, device=bits.device, dtype=torch.int32))
-        packed = (expanded.to(torch.int32) * weights).sum(dim=1).to(torch.uint8)
+        shifts = torch.arange(8, device=bits.device, dtype=torch.uint8)
+        flags = ((bits.unsqueeze(1) >> shifts) & 1).contiguous()
+        dist.all_reduce(flags, op=dist.ReduceOp.MAX)
+        packed = (flags.to(torch.int32) << shifts.to(torch.int32)).sum(dim=1).to(torch.uint8)
         return packed.view(torch.int32)
+
+
+class FrameRenderer(StripeGather):
+    """GpuCamera + StripeGather: what one rank does per frame."""
+
+    def __init__(self, cam, rank: int, world: int, stripe: int = STRIPE_ROWS):
+        super().__init__(cam.settings.width, cam.settings.height, rank, world, cam.device, stripe)
+        self.cam = cam
+
+    def render(self, prepare=True, want=("rgba8",)):
+        """Render this rank's stripes into its band (one kernel launch)."""
+        out = {"rgba8": self.my_band()}
+        return self.cam.render(stripes=(self.stripe, self.world, self.rank), want=want, prepare=prepare, out=out)
 
     def frame_to_host(self, pos, rot, chunk_res, host_rgba8):
         """The call a user of the engine makes per frame, with HOST buffers: camera + per-chunk LOD table +
