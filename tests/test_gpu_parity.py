@@ -21,7 +21,8 @@ def gpu_case(case, want=("rgba8", "mean", "ray0", "visited", "counters"), **over
     out = cam.render(pixels=case["pixels"], want=want)
     torch.cuda.synchronize()
     res = {k: v.cpu().numpy() for k, v in out.items() if k != "visited"}
-    res["visited"] = cam.visited_slots(out["visited"])
+    if "visited" in out:
+        res["visited"] = cam.visited_slots(out["visited"])
     cam.close()
     return res
 
