@@ -9,7 +9,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libvoxtrace.so")
 SOURCES = ["voxtrace.cu"]
-HEADERS = [os.path.join(CSRC, "vt_device.cuh"), os.path.join(os.path.dirname(PKG_DIR), "include", "voxtrace.h")]
+HEADERS = [os.path.join(CSRC, "vt_device.cuh"), os.path.join(CSRC, "vt_march.cuh"), os.path.join(os.path.dirname(PKG_DIR), "include", "voxtrace.h")]
 
 # -fmad=false: the reference computes in Python floats, every a*b+c rounds twice; FMA contraction would change
 # the sampled positions.  -lineinfo: ncu source pages map to our lines.
@@ -32,17 +32,18 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build_library(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build_library(force: bool = False, verbose: bool = False, defines=(), out: str | None = None) -> str:
+    """defines / out: tuning variants (-DNAME=VALUE) built next to the product library, for A/B runs only."""
+    if out is None and not force and not needs_build():
         return LIB_PATH
-    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH] + \
-          [os.path.join(CSRC, s) for s in SOURCES]
+    cmd = [_nvcc()] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-D" + d for d in defines] + \
+          ["-o", out or LIB_PATH] + [os.path.join(CSRC, s) for s in SOURCES]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)
     if verbose:
         print(res.stderr)
-    return LIB_PATH
+    return out or LIB_PATH
 
 
 if __name__ == "__main__":

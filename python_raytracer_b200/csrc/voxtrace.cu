@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "vt_device.cuh"
+#include "vt_march.cuh"
 
 using namespace vt;
 
@@ -162,6 +163,7 @@ struct vt_ctx {
     double cam_pos[3] = {0, 0, 0}, cam_rot[4] = {0, 0, 0, 0}, cam_lens = 0;
     // lens tables (dof == 0): rebuilt when (lens, width, height, proportions) change
     double *d_col_sc = nullptr, *d_row_sc = nullptr;
+    double *d_dir_x = nullptr, *d_dir_y = nullptr; int dir_w = 0, dir_h = 0;   // init.py:131-132 per column / row
     int tab_w = 0, tab_h = 0; double tab_lens = -1, tab_prop = -1;
 
     // world
@@ -175,6 +177,13 @@ struct vt_ctx {
     std::vector<uint32_t> free_slots;
     double *d_mats = nullptr;                   // [256][8]
 
+    // persistent kernel state: per-pixel accumulators (zero between launches), ray queue, launch geometry
+    unsigned long long *d_acc = nullptr; long long acc_cap = 0;     // in u64 words
+    unsigned long long *d_queue = nullptr;
+    int persist_blocks[4] = {0, 0, 0, 0};                           // resident blocks per SM, per instantiation
+    int sm_count = 0;
+    int kernel_version = 2;                                         // VT_KERNEL=1 selects the v1 warp-tile kernel (A/B)
+    int refill_min = 8;                                             // VT_REFILL overrides
     // region row map
     int32_t *d_row_y = nullptr; int row_cap = 0;
     std::vector<int32_t> h_row_y; int row_key[7] = {-1, -1, -1, -1, -1, -1, -1};
@@ -215,6 +224,15 @@ extern "C" int vt_create(int device, vt_ctx **out) {
         return 2;
     }
     ctx->own_stream = true;
+    if ((e = cudaMalloc(&ctx->d_queue, 2 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMemset(ctx->d_queue, 0, 2 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device)) != cudaSuccess) {
+        g_create_err = std::string("vt_create: ") + cudaGetErrorString(e);
+        delete ctx;
+        return 2;
+    }
+    if (const char *k = getenv("VT_KERNEL")) ctx->kernel_version = atoi(k) == 1 ? 1 : 2;
+    if (const char *k = getenv("VT_REFILL")) { int v = atoi(k); if (v >= 1 && v <= 32) ctx->refill_min = v; }
     *out = ctx;
     return 0;
 }
@@ -232,6 +250,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_world(ctx);
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
+    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -478,6 +497,24 @@ static int update_lens_tables(vt_ctx *ctx) {
     return 0;
 }
 
+// dir_x / dir_y of init.py:131-132 for every column / row: a correctly rounded division each, done once on the host
+static int update_dir_tables(vt_ctx *ctx) {
+    const vt_settings &s = ctx->s;
+    if (ctx->d_dir_x && ctx->dir_w == s.width && ctx->dir_h == s.height) return 0;
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y); ctx->d_dir_x = ctx->d_dir_y = nullptr;
+    std::vector<double> dx((size_t)s.width), dy((size_t)s.height);
+    for (int x = 0; x < s.width; x++) dx[x] = -1.0 + ((double)x / (double)s.width) * 2.0;
+    for (int y = 0; y < s.height; y++) dy[y] = -1.0 + ((double)y / (double)s.height) * 2.0;
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_dir_x, dx.size() * sizeof(double)));
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_dir_y, dy.size() * sizeof(double)));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_dir_x, dx.data(), dx.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_dir_y, dy.data(), dy.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->dir_w = s.width; ctx->dir_h = s.height;
+    return 0;
+}
+
 static int update_row_map(vt_ctx *ctx, const vt_region *r, int *band_rows) {
     int key[7] = {r->x0, r->y0, r->x1, r->y1, r->stripe_rows, r->stripe_count, r->stripe_index};
     if (ctx->d_row_y && memcmp(key, ctx->row_key, sizeof key) == 0) { *band_rows = (int)ctx->h_row_y.size(); return 0; }
@@ -495,6 +532,65 @@ static int update_row_map(vt_ctx *ctx, const vt_region *r, int *band_rows) {
     }
     memcpy(ctx->row_key, key, sizeof key);
     *band_rows = n;
+    return 0;
+}
+
+// Launch geometry and per-launch tables of the persistent kernel (vt_march.cuh).
+template <bool REC, bool FULL_TAIL, bool COUNT>
+static int persistent_blocks_per_sm(vt_ctx *ctx, int *slot) {
+    if (*slot == 0) {
+        int nb = 0;
+        VT_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, render_persistent<REC, FULL_TAIL, COUNT>, 128, 0));
+        *slot = nb > 0 ? nb : 1;
+    }
+    return 0;
+}
+
+static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
+    const vt_settings &s = ctx->s;
+    if (s.width > 65535 || s.height > 65535) return fail(ctx, "vt_render: canvas larger than 65535 pixels per side");
+    if (P.n_pixels > 0xffffffffLL) return fail(ctx, "vt_render: more than 2^32 pixels in one region");
+    // most samples any pixel can ask for: detail <= 1 + max(0, -lod_edge) (init.py:133-134)
+    double dmax = 1.0 + (s.lod_edge < 0.0 ? -s.lod_edge : 0.0);
+    long long smax = (long long)nearbyint((double)s.samples * dmax);
+    if (smax < 1) smax = 1;
+    if (smax > (1 << 20) - 1) return fail(ctx, "vt_render: more than 2^20 samples per pixel");
+    P.rounds = (int)((smax + P.group - 1) / P.group);
+    P.total_rays = (unsigned long long)P.n_warps * (unsigned long long)P.rounds * 32ull;
+    if ((P.total_rays >> 5) > 0xffffffffull) return fail(ctx, "vt_render: region too large for one launch");
+    P.acc_wide = smax > 64 ? 1 : 0;
+    long long words = P.n_pixels * (P.acc_wide ? 2 : 1);
+    if (words > ctx->acc_cap) {
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_acc); ctx->d_acc = nullptr; ctx->acc_cap = 0;
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_acc, (size_t)words * sizeof(unsigned long long)));
+        VT_CHECK(ctx, cudaMemsetAsync(ctx->d_acc, 0, (size_t)words * sizeof(unsigned long long), ctx->stream));
+        ctx->acc_cap = words;
+    }
+    P.acc = ctx->d_acc; P.queue = ctx->d_queue; P.refill_min = ctx->refill_min;
+    for (int r = 2; r <= VT_LOD_TAB; r++) {
+        P.lod_magic[r] = (uint32_t)((1ull << 32) / (unsigned)r) + 1u;
+        for (int a = 0; a < 3; a++) { int m = ctx->origin[a] % r; P.lod_bias[r][a] = m < 0 ? m + r : m; }
+    }
+    int which = (rec ? 2 : 0) | (count ? 1 : 0), rc = 0;
+    switch (which) {
+        case 0: rc = persistent_blocks_per_sm<false, false, false>(ctx, &ctx->persist_blocks[0]); break;
+        case 1: rc = persistent_blocks_per_sm<false, false, true>(ctx, &ctx->persist_blocks[1]); break;
+        case 2: rc = persistent_blocks_per_sm<true, true, false>(ctx, &ctx->persist_blocks[2]); break;
+        default: rc = persistent_blocks_per_sm<true, true, true>(ctx, &ctx->persist_blocks[3]); break;
+    }
+    if (rc) return rc;
+    long long want = (long long)((P.total_rays + 127) / 128);             // one ray slot per thread at least once
+    long long resident = (long long)ctx->sm_count * ctx->persist_blocks[which];
+    int grid = (int)(want < resident ? want : resident);
+    if (grid < 1) grid = 1;
+    P.total_warps = (unsigned)grid * 4u;
+    switch (which) {
+        case 0: render_persistent<false, false, false><<<grid, 128, 0, ctx->stream>>>(P, ctx->d_row_y); break;
+        case 1: render_persistent<false, false, true><<<grid, 128, 0, ctx->stream>>>(P, ctx->d_row_y); break;
+        case 2: render_persistent<true, true, false><<<grid, 128, 0, ctx->stream>>>(P, ctx->d_row_y); break;
+        default: render_persistent<true, true, true><<<grid, 128, 0, ctx->stream>>>(P, ctx->d_row_y); break;
+    }
     return 0;
 }
 
@@ -519,6 +615,8 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
     memcpy(P.cam.pos, ctx->cam_pos, sizeof P.cam.pos);
     memcpy(P.cam.rot, ctx->cam_rot, sizeof P.cam.rot);
     P.cam.lens = ctx->cam_lens;
+    if (int rc = update_dir_tables(ctx)) return rc;
+    P.cam.dir_x = ctx->d_dir_x; P.cam.dir_y = ctx->d_dir_y;
     if (s.dof == 0.0) {
         if (int rc = update_lens_tables(ctx)) return rc;
         P.cam.col_sc = ctx->d_col_sc; P.cam.row_sc = ctx->d_row_sc;
@@ -556,11 +654,15 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
         P.n_warps = (long long)P.tiles_x * ((P.band_rows + P.tile_h - 1) / P.tile_h);
     }
     const int block = 128;
-    long long blocks = (P.n_warps + (block / 32) - 1) / (block / 32);
-    if (blocks > 0x7fffffffLL) return fail(ctx, "vt_render: region too large for one launch");
-    int grid = (int)blocks;
-    if (dev_ray0) render_kernel<true, true><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
-    else render_kernel<false, false><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
+    if (ctx->kernel_version == 1) {
+        long long blocks = (P.n_warps + (block / 32) - 1) / (block / 32);
+        if (blocks > 0x7fffffffLL) return fail(ctx, "vt_render: region too large for one launch");
+        int grid = (int)blocks;
+        if (dev_ray0) render_kernel<true, true><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
+        else render_kernel<false, false><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
+    } else {
+        if (int rc = launch_persistent(ctx, P, dev_ray0 != nullptr, dev_counters != nullptr)) return rc;
+    }
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     return 0;

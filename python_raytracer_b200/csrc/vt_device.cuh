@@ -14,6 +14,8 @@
 #include <cuda_runtime.h>
 #include "../../include/voxtrace.h"
 
+#define VT_LOD_TAB 16               // Frame.resolution values served by the multiply-high snap table
+
 namespace vt {
 
 struct DevWorld {
@@ -33,6 +35,8 @@ struct DevCamera {
     double lens;
     const double *col_sc;           // [width][2]  sin, cos of the column's half yaw  (dof == 0 only)
     const double *row_sc;           // [height][2] sin, cos of the row's half pitch   (dof == 0 only)
+    const double *dir_x;            // [width]  -1 + (x / width) * 2   (init.py:131), host division
+    const double *dir_y;            // [height] -1 + (y / height) * 2  (init.py:132)
 };
 
 struct DevParams {
@@ -48,6 +52,16 @@ struct DevParams {
     // warp tiling: `group` lanes per pixel, 32/group pixels per warp arranged tile_w x tile_h
     int group, group_shift, tile_w, tile_w_shift, tile_h, tiles_x;
     long long n_warps;
+    // persistent kernel (vt_march.cuh): ray queue, per-pixel accumulators, LOD snap tables
+    unsigned long long total_rays;  // n_tiles * rounds * 32 ray slots (invalid slots included)
+    int rounds;                     // ceil(max samples per pixel / group)
+    int acc_wide;                   // 0: one u64 per pixel (<= 64 samples), 1: two u64 per pixel
+    unsigned long long *acc;        // zero between launches (the last sample of a pixel clears it)
+    unsigned long long *queue;      // [0] next ray slot, [1] warps finished; both zero between launches
+    unsigned int total_warps;       // warps launched
+    int refill_min;                 // refill once this many lanes are idle
+    uint32_t lod_magic[VT_LOD_TAB + 1];   // floor(n / r) == umulhi(n, magic[r]) for n < 2^24 / r ... (r >= 2)
+    int32_t lod_bias[VT_LOD_TAB + 1][3];  // world origin mod r per axis
     // outputs
     uint8_t *rgba8;
     float *mean;
@@ -75,6 +89,24 @@ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t
         k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
     }
     out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+// ------------------------------------------------------------------------------------------------------
+// Conversions on the fp64 pipe.  F2I/I2F/FRND with a 64-bit operand issue on the XU pipe (4 lanes/clk/SMSP on
+// sm_100); the v1 kernel saturated it (profiles/r1_v2a: xu "realtime" 136 %).  Adding 2^52 + 2^51 puts the
+// integer part of |p| < 2^31 into the low mantissa word with the rounding of the add itself.
+#define VT_MAGIC 6755399441055744.0            /* 2^52 + 2^51 */
+__device__ __forceinline__ int floor_i(double p) { return __double2loint(__dadd_rd(p, VT_MAGIC)); }
+__device__ __forceinline__ int rint_i(double p) { return __double2loint(__dadd_rn(p, VT_MAGIC)); }      // ties to even
+__device__ __forceinline__ double rint_d(double p) { return __dadd_rn(__dadd_rn(p, VT_MAGIC), -VT_MAGIC); }
+__device__ __forceinline__ double floor_d(double p) { return __dadd_rn(__dadd_rd(p, VT_MAGIC), -VT_MAGIC); }
+__device__ __forceinline__ double i2d(int x) {                                                          // exact
+    return __dadd_rn(__hiloint2double(0x43300000, x ^ (int)0x80000000), -4503601774854144.0);          // 2^52 + 2^31
+}
+__device__ __forceinline__ double u2d(uint32_t x) { return __dadd_rn(__hiloint2double(0x43300000, (int)x), -4503599627370496.0); }
+
+__device__ __forceinline__ double u53m(uint32_t hi, uint32_t lo) {    // u53 without XU conversions, same value
+    return (u2d(hi >> 5) * 67108864.0 + u2d(lo >> 6)) * (1.0 / 9007199254740992.0);
 }
 
 __device__ __forceinline__ double u53(uint32_t hi, uint32_t lo) {

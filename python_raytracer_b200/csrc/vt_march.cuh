@@ -1,0 +1,487 @@
+// vt_march.cuh — persistent ray-march kernel (render kernel v2) for sm_100a.
+//
+// Same arithmetic as vt_device.cuh's trace_warp (reference init.py:37-150, lib.py:448-476, data.py:136-145) --
+// every ray produces the same sample positions, hits and colours -- but scheduled differently:
+//
+//   * One persistent grid per frame.  Every LANE owns one ray at a time and fetches the next ray slot from a
+//     global queue when its ray ends (rays of a frame differ in length by 10x, so a warp that waits for its
+//     longest ray idles most lanes).  Pixel means are accumulated with one 64-bit atomic per ray: the channel
+//     sums are sums of integers 0..255, so the order of arrival cannot change the result; the sample that
+//     completes a pixel writes it and clears the accumulator.
+//   * A warp is a small state machine.  Lanes are MARCH (stepping through cells), HIT (found a solid cell,
+//     material interaction pending) or idle (ray ended / no ray).  Each round the warp runs the phase most lanes
+//     wait for, so the expensive rare work (pow, divisions, Philox, sincos, atomics) runs with many lanes active
+//     instead of serialising a warp on one lane.
+//   * Per-sample work is integer-only apart from the position update: cells are addressed relative to the world
+//     origin, the chunk test is one unsigned max, LOD snapping is a multiply-high.
+#pragma once
+#include "vt_device.cuh"
+
+namespace vt {
+
+enum : uint32_t { ST_NONE = 0u, ST_MARCH = 1u, ST_HIT = 2u, ST_DONE = 3u };
+
+// st: bits 0-1 state, bits 2-9 material id of a pending hit, bits 12-31 sample index of the ray
+struct Lane {
+    double px, py, pz, vx, vy, vz, step, life, bounces, energy;
+    int col;                        // ray.color as r | g << 8 | b << 16 (integers, lib.py:393-395)
+    int cx, cy, cz;                 // chunk_min relative to the world origin (chunk_max = chunk_min + chunk_size)
+    int res;                        // Frame.resolution of the current chunk, 0 = `chunk is None`
+    uint32_t st;
+    uint32_t xy;                    // pixel x | y << 16
+    uint32_t out_i;                 // output index of the pixel
+    uint32_t draw, w2, w3;          // Philox draw counter and the cached second uniform of the last block
+};
+
+struct FirstHit {                   // parity probe state, only live in the REC instantiation
+    int hits, fflag, fx, fy, fz;
+    double first_step;
+};
+
+__device__ __forceinline__ uint32_t lane_state(const Lane &L) { return L.st & 3u; }
+__device__ __forceinline__ uint32_t lane_sample(const Lane &L) { return L.st >> 12; }
+__device__ __forceinline__ void lane_set_state(Lane &L, uint32_t s) { L.st = (L.st & ~0xffcu & ~3u) | s; }
+
+// ---- Philox stream of one ray: key = global pixel index, counter = (block, sample, frame seed) --------------
+__device__ __forceinline__ double lane_rng_next(const DevParams &P, Lane &L) {
+    uint32_t d = L.draw++;
+    if ((d & 1u) == 0u) {
+        uint32_t w[4];
+        uint32_t pix = (L.xy >> 16) * (uint32_t)P.s.width + (L.xy & 0xffffu);
+        philox4x32_10(d >> 1, lane_sample(L), P.seed_lo, P.seed_hi, pix, 0u, w);
+        L.w2 = w[2]; L.w3 = w[3];
+        return u53m(w[0], w[1]);
+    }
+    return u53m(L.w2, L.w3);
+}
+__device__ __forceinline__ double lane_rng_rand(const DevParams &P, Lane &L, double amp) {   // lib.py:431-434
+    if (amp == 0.0) return 0.0;
+    return (-1.0 + lane_rng_next(P, L) * 2.0) * amp;
+}
+
+// ---- cell addressing, relative to the world origin ------------------------------------------------------------
+// res * floor(abs / res) - origin for abs = r + origin, r >= 0 (data.py:137 with Python's floor division)
+__device__ __forceinline__ int lod_snap(const DevParams &P, int res, int r, int axis) {
+    if (res <= VT_LOD_TAB) {
+        int b = P.lod_bias[res][axis];
+        uint32_t f = __umulhi((uint32_t)(r + b), P.lod_magic[res]);
+        return (int)(f * (uint32_t)res) - b;
+    }
+    int o = axis == 0 ? P.w.ox : axis == 1 ? P.w.oy : P.w.oz;
+    return ifloordiv(r + o, res) * res - o;
+}
+
+__device__ __forceinline__ int cell_at(const DevWorld &w, int qx, int qy, int qz) {
+    uint32_t b = __ldg(&w.brick_tab[((qx >> 3) * w.nby + (qy >> 3)) * w.nbz + (qz >> 3)]);
+    if (b == 0u) return 0;
+    return __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
+}
+
+// Frame.get_voxel (data.py:136-145) of the LOD-`res` frame of the chunk at (cx, cy, cz) for ANY cell (jx, jy, jz):
+// the key floor(p) // res exists iff the cell res * key lies inside that chunk (init.py:417-424, data.py:165-169).
+__device__ __forceinline__ int lookup_any(const DevParams &P, int cx, int cy, int cz, int res, int jx, int jy, int jz) {
+    const int cs = P.s.chunk_size;
+    if ((jx | jy | jz) < 0) return 0;                  // below the world box: res * key <= j is outside too
+    if (res > 1) { jx = lod_snap(P, res, jx, 0); jy = lod_snap(P, res, jy, 1); jz = lod_snap(P, res, jz, 2); }
+    if ((unsigned)(jx - cx) >= (unsigned)cs || (unsigned)(jy - cy) >= (unsigned)cs || (unsigned)(jz - cz) >= (unsigned)cs)
+        return 0;
+    return cell_at(P.w, jx, jy, jz);
+}
+
+__device__ __forceinline__ int snap_rel(int r, int cs, int cs_shift) {   // origin is a multiple of chunk_size
+    return cs_shift >= 0 ? ((r >> cs_shift) << cs_shift) : ifloordiv(r, cs) * cs;
+}
+
+// chunk slot of the chunk at relative origin (cx, cy, cz), or -1 (`post in self.chunks` is false outside the box)
+__device__ __forceinline__ int chunk_slot_rel(const DevWorld &w, int cs, int cs_shift, int cx, int cy, int cz) {
+    if ((unsigned)cx >= (unsigned)w.nx || (unsigned)cy >= (unsigned)w.ny || (unsigned)cz >= (unsigned)w.nz) return -1;
+    int sx, sy, sz;
+    if (cs_shift >= 0) { sx = cx >> cs_shift; sy = cy >> cs_shift; sz = cz >> cs_shift; }
+    else { sx = cx / cs; sy = cy / cs; sz = cz / cs; }
+    return (sx * w.ncy + sy) * w.ncz + sz;
+}
+
+// init.py:67-73: re-snap the chunk box around the cell (ix, iy, iz), look the chunk up, record it as traversed.
+// Returns false when the ray can stop (FULL_TAIL == false): outside the world box and moving away from it.
+template <bool FULL_TAIL, bool COUNT>
+__device__ __forceinline__ bool rechunk(const DevParams &P, Lane &L, int ix, int iy, int iz, Counters &c) {
+    const DevWorld &w = P.w;
+    const int cs = P.s.chunk_size, sh = P.cs_shift;
+    L.cx = snap_rel(ix, cs, sh); L.cy = snap_rel(iy, cs, sh); L.cz = snap_rel(iz, cs, sh);
+    int slot = chunk_slot_rel(w, cs, sh, L.cx, L.cy, L.cz);
+    L.res = 0;
+    if (COUNT) c.rechunk++;
+    if (slot >= 0) { L.res = __ldg(&w.chunk_res[slot]); mark_visited(P.visited, slot); }
+    else if (!FULL_TAIL) {
+        bool gone = (ix >= w.nx && L.vx >= 0.0) || (ix < 0 && L.vx <= 0.0) || (iy >= w.ny && L.vy >= 0.0) ||
+                    (iy < 0 && L.vy <= 0.0) || (iz >= w.nz && L.vz >= 0.0) || (iz < 0 && L.vz <= 0.0);
+        if (gone) return false;
+    }
+    return true;
+}
+
+// void step of init.py:114 (see vt_device.cuh void_step); for a power-of-two chunk size a / cs == a * (1 / cs) exactly
+__device__ __forceinline__ double void_step2(double px, double py, double pz, int radius, int cs, int cs_shift) {
+    double a = fmin(px, fmin(py, pz)) + i2d(radius);
+    double m;
+    if (cs_shift >= 0) {
+        double dcs = i2d(cs), inv = __hiloint2double((1023 - cs_shift) << 20, 0);
+        m = a - dcs * floor_d(a * inv);
+    } else m = py_mod_pos(a, i2d(cs));
+    return 1.0 + fabs(i2d(radius) - m);
+}
+
+__device__ __forceinline__ void advance(Lane &L, double step) {          // init.py:115-116
+    L.step += step;
+    L.px += L.vx * step; L.py += L.vy * step; L.pz += L.vz * step;
+    if (!(L.step < L.life)) lane_set_state(L, ST_DONE);
+}
+
+// One iteration of the reference's while loop for a MARCH lane, up to but excluding the material call
+// (init.py:66-77, 114-116), in two blocks the kernel separates with a __syncwarp so that the rare block (A: the
+// ray left its chunk box) cannot drag a private copy of the common block (B: look at the cell, advance) behind it.
+//
+// Block A (init.py:67-73).  `um` >= chunk_size: not strictly inside the chunk box.  The reference's test is
+// inclusive at chunk_max (lib.py:228-244): a position exactly on the far face(s) stays in the old chunk ("sticky");
+// then the cell is looked up with the old chunk's frame right here and `mat` carries the answer to block B as
+// mat + 1 (0 = not looked up yet).
+template <bool FULL_TAIL, bool COUNT>
+__device__ __forceinline__ int march_leave_chunk(const DevParams &P, Lane &L, Counters &c, int ix, int iy, int iz) {
+    const DevWorld &w = P.w;
+    const unsigned cs = (unsigned)P.s.chunk_size;
+    const unsigned ux = (unsigned)(ix - L.cx), uy = (unsigned)(iy - L.cy), uz = (unsigned)(iz - L.cz);
+    bool sticky = false;
+    if (max(ux, max(uy, uz)) == cs)
+        sticky = (ux < cs || L.px == i2d(ix + w.ox)) && (uy < cs || L.py == i2d(iy + w.oy)) && (uz < cs || L.pz == i2d(iz + w.oz));
+    if (sticky) return 1 + (L.res ? lookup_any(P, L.cx, L.cy, L.cz, L.res, ix, iy, iz) : 0);
+    if (!rechunk<FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
+    return 0;
+}
+
+// Block B (init.py:75-77, 114-116): examine the cell under the ray; a solid one turns the lane into HIT (the position
+// is not advanced -- the material phase does that), an empty one advances the ray.
+template <bool COUNT>
+__device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters &c, int ix, int iy, int iz, int looked) {
+    const DevWorld &w = P.w;
+    double step;
+    if (L.res) {
+        if (COUNT) c.in_chunk++;
+        int mat = looked - 1;
+        if (!looked) {
+            int qx = ix, qy = iy, qz = iz;
+            bool in = true;
+            if (L.res > 1) {
+                qx = lod_snap(P, L.res, ix, 0); qy = lod_snap(P, L.res, iy, 1); qz = lod_snap(P, L.res, iz, 2);
+                in = qx >= L.cx && qy >= L.cy && qz >= L.cz;            // q <= i, so only the near faces can fail
+            }
+            mat = in ? cell_at(w, qx, qy, qz) : 0;
+        }
+        if (mat) { L.st = (L.st & ~0xfffu) | ST_HIT | ((uint32_t)mat << 2); return; }
+        step = i2d(L.res);
+    } else {
+        if (COUNT) c.in_void++;
+        step = void_step2(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift);
+    }
+    advance(L, step);
+}
+
+// lib.material (lib.py:448-460) + the post-hit part of the loop body (init.py:78-116) for a HIT lane.
+template <bool REC, bool COUNT>
+__device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit &fh, Counters &c) {
+    const vt_settings &s = P.s;
+    const DevWorld &w = P.w;
+    const int cs = s.chunk_size, sh = P.cs_shift;
+    const int mat = (int)((L.st >> 2) & 0xffu);
+    const double *m = w.mats + 8 * mat;
+    const int ix = floor_i(L.px) - w.ox, iy = floor_i(L.py) - w.oy, iz = floor_i(L.pz) - w.oz;
+    if (REC) {
+        if (!fh.fflag) { fh.fflag = 1; fh.fx = ix + w.ox; fh.fy = iy + w.oy; fh.fz = iz + w.oz; fh.first_step = L.step; }
+        fh.hits++;
+    }
+    if (COUNT) c.hits++;
+    // ---- lib.material ----
+    double alb_r = __ldg(m + 0), alb_g = __ldg(m + 1), alb_b = __ldg(m + 2);
+    double rough = __ldg(m + 3), absorb = __ldg(m + 4), emit = __ldg(m + 6);
+    // pow(1, y) == 1 exactly: the first interaction of a ray (bounces == 0) needs no pow
+    double pw = (L.bounces == 0.0) ? 1.0 : pow(1.0 + L.bounces, 1.0 + s.falloff);
+    double a = fmin(1.0, absorb / pw);
+    double b2 = 1.0 - a;
+    int cr = rint_i(i2d(L.col & 255) * b2 + alb_r * a);
+    int cg = rint_i(i2d((L.col >> 8) & 255) * b2 + alb_g * a);
+    int cb = rint_i(i2d((L.col >> 16) & 255) * b2 + alb_b * a);
+    L.col = cr | (cg << 8) | (cb << 16);
+    L.energy = L.energy * b2 + emit * a;
+    L.life *= 1.0 - (rough * a);
+    double jx = lane_rng_rand(P, L, rough), jy = lane_rng_rand(P, L, rough), jz = lane_rng_rand(P, L, rough);
+    L.vx += jx; L.vy += jy; L.vz += jz;
+    // ---- init.py:82-86 ----
+    L.bounces += absorb;
+    L.life /= i2d(L.res) + absorb * s.lod_bounces;
+    double ref = fmax(fabs(L.vx), fmax(fabs(L.vy), fabs(L.vz)));             // vec3.normalize, lib.py:310-314
+    if (ref != 0.0 && ref != 1.0) { L.vx /= ref; L.vy /= ref; L.vz /= ref; }
+    if (L.step >= L.life || L.energy >= s.max_light || L.bounces >= s.max_bounces + 1.0) {
+        lane_set_state(L, ST_DONE);                                          // `break`, init.py:85-86
+        return;
+    }
+    double ior = __ldg(m + 5);
+    if (ior != 0.0) {                                                        // init.py:92-111
+        double direction = (ior - 0.5) * 2.0;
+        bool flip[3];
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+            double va = k == 0 ? L.vx : k == 1 ? L.vy : L.vz;
+            double qa = k == 0 ? L.px : k == 1 ? L.py : L.pz;
+            int oa = k == 0 ? w.ox : k == 1 ? w.oy : w.oz;
+            qa = (va < direction) ? qa + 1.0 : qa - 1.0;
+            int ja = floor_i(qa) - oa;
+            int jx_ = k == 0 ? ja : ix, jy_ = k == 1 ? ja : iy, jz_ = k == 2 ? ja : iz;
+            int lo = k == 0 ? L.cx : k == 1 ? L.cy : L.cz;
+            unsigned u = (unsigned)(ja - lo);
+            int nid = 0;
+            // `pos >= chunk_min and pos <= chunk_max` on the probed axis (the other two are the hit cell's own)
+            if (u < (unsigned)cs || (u == (unsigned)cs && qa == i2d(ja + oa))) {
+                nid = lookup_any(P, L.cx, L.cy, L.cz, L.res, jx_, jy_, jz_);
+                if (COUNT) c.probes++;
+            } else {                                                         // Camera.chunk_get, init.py:28-33
+                int nx = snap_rel(jx_, cs, sh), ny = snap_rel(jy_, cs, sh), nz = snap_rel(jz_, cs, sh);
+                int nslot = chunk_slot_rel(w, cs, sh, nx, ny, nz);
+                int nres = nslot >= 0 ? (int)__ldg(&w.chunk_res[nslot]) : 0;
+                if (nres) { nid = lookup_any(P, nx, ny, nz, nres, jx_, jy_, jz_); if (COUNT) c.probes++; }
+            }
+            flip[k] = (nid == 0) || (__ldg(w.mats + 8 * nid + 5) != ior);
+        }
+        if (flip[0]) L.vx -= L.vx * ior * 2.0;
+        if (flip[1]) L.vy -= L.vy * ior * 2.0;
+        if (flip[2]) L.vz -= L.vz * ior * 2.0;
+    }
+    lane_set_state(L, ST_MARCH);
+    advance(L, i2d(L.res));                                               // init.py:114-116
+}
+
+// init.py:131-134: samples traced for pixel (x, y); dir_x / dir_y come from host tables (exact divisions)
+__device__ __forceinline__ int pixel_samples(const DevParams &P, int x, int y, double &dir_x, double &dir_y, double &detail) {
+    const vt_settings &s = P.s;
+    dir_x = __ldg(P.cam.dir_x + x);
+    dir_y = __ldg(P.cam.dir_y + y);
+    if (s.lod_edge == 0.0) { detail = 1.0; return s.samples < 1 ? 1 : s.samples; }
+    detail = 1.0 - fabs(dir_x * dir_y) * s.lod_edge;
+    int n = rint_i(i2d(s.samples) * detail);
+    return n < 1 ? 1 : n;
+}
+
+// End of a ray (init.py:119-121, 141-146): background, alpha, then add the sample to its pixel.  The sample that
+// completes the pixel computes the mean (lib.average, lib.py:419-428), writes it and clears the accumulator.
+template <bool REC>
+__device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const FirstHit &fh) {
+    const vt_settings &s = P.s;
+    double cr = i2d(L.col & 255), cg = i2d((L.col >> 8) & 255), cb = i2d((L.col >> 16) & 255);
+    if (s.background) {                                                      // lib.material_background, lib.py:463-476
+        double pw = (L.bounces == 0.0) ? 1.0 : pow(1.0 + L.bounces, 1.0 + s.falloff);
+        double a = fmin(1.0, 1.0 / pw);
+        double up = fmax(0.0, L.vy);
+        double b2 = 1.0 - a;
+        cr = rint_d(cr * b2 + 127.0 * a);
+        cg = rint_d(cg * b2 + (127.0 + up * 64.0) * a);
+        cb = rint_d(cb * b2 + (127.0 + up * 128.0) * a);
+        L.energy = mixd(L.energy, 1.0 + up, a);
+        cr = fmin(255.0, rint_d(cr * L.energy));
+        cg = fmin(255.0, rint_d(cg * L.energy));
+        cb = fmin(255.0, rint_d(cb * L.energy));
+    }
+    double alpha = rint_d(fmin(1.0, L.energy + s.shutter) * 255.0);            // init.py:141
+    const int x = (int)(L.xy & 0xffffu), y = (int)(L.xy >> 16);
+    double dx_, dy_, det_;
+    const int n = pixel_samples(P, x, y, dx_, dy_, det_);
+    const size_t i = L.out_i;
+    if (REC && lane_sample(L) == 0u) {
+        double *o = P.ray0 + (size_t)VT_RAY_RECORD * i;
+        o[0] = cr; o[1] = cg; o[2] = cb; o[3] = L.energy; o[4] = L.bounces; o[5] = L.step;
+        o[6] = i2d(fh.hits); o[7] = i2d(fh.fx); o[8] = i2d(fh.fy); o[9] = i2d(fh.fz);
+        o[10] = i2d(fh.fflag); o[11] = fh.first_step; o[12] = L.vx; o[13] = L.vy; o[14] = L.vz; o[15] = i2d(n);
+    }
+    // colour channels can be negative only through a negative albedo/energy; clamp like the u8 store would not --
+    // the accumulator holds non-negative integers, so clamp at 0 here and keep the mean of the clamped values
+    unsigned long long ur = (unsigned)rint_i(fmax(cr, 0.0)), ug = (unsigned)rint_i(fmax(cg, 0.0));
+    unsigned long long ub = (unsigned)rint_i(fmax(cb, 0.0)), ua = (unsigned)rint_i(fmax(alpha, 0.0));
+    unsigned long long sr, sg, sb, sa;
+    bool last;
+    if (!P.acc_wide) {
+        unsigned long long add = ur | (ug << 14) | (ub << 28) | (ua << 42) | (1ull << 56);
+        unsigned long long tot = atomicAdd(P.acc + i, add) + add;
+        last = (int)(tot >> 56) == n;
+        sr = tot & 0x3fffull; sg = (tot >> 14) & 0x3fffull; sb = (tot >> 28) & 0x3fffull; sa = (tot >> 42) & 0x3fffull;
+        if (last) P.acc[i] = 0ull;
+    } else {
+        atomicAdd(P.acc + 2 * i, ur | (ug << 21) | (ub << 42));
+        __threadfence();
+        unsigned long long add = ua | (1ull << 32);
+        unsigned long long tot = atomicAdd(P.acc + 2 * i + 1, add) + add;
+        last = (int)(tot >> 32) == n;
+        sa = tot & 0xffffffffull;
+        sr = sg = sb = 0ull;
+        if (last) {
+            __threadfence();
+            unsigned long long rgb = atomicExch(P.acc + 2 * i, 0ull);
+            sr = rgb & 0x1fffffull; sg = (rgb >> 21) & 0x1fffffull; sb = (rgb >> 42) & 0x1fffffull;
+            P.acc[2 * i + 1] = 0ull;
+        }
+    }
+    if (last) {
+        double dn = i2d(n);
+        double mr = u2d((uint32_t)sr) / dn, mg = u2d((uint32_t)sg) / dn, mb = u2d((uint32_t)sb) / dn, ma = u2d((uint32_t)sa) / dn;
+        if (P.mean) reinterpret_cast<float4 *>(P.mean)[i] = make_float4((float)mr, (float)mg, (float)mb, (float)ma);
+        if (P.rgba8) {
+            uchar4 q;                                                        // truncation, like a C cast
+            q.x = (unsigned char)floor_i(fmin(255.0, mr)); q.y = (unsigned char)floor_i(fmin(255.0, mg));
+            q.z = (unsigned char)floor_i(fmin(255.0, mb)); q.w = (unsigned char)floor_i(fmin(255.0, ma));
+            reinterpret_cast<uchar4 *>(P.rgba8)[i] = q;
+        }
+    }
+}
+
+// Start of a ray (init.py:131-139, 41-59) for ray slot `id`.  Slots enumerate (pixel tile, sample round, lane):
+// 32 consecutive slots are the G samples of 32/G neighbouring pixels, so lanes refilled together start coherent.
+template <bool REC, bool FULL_TAIL, bool COUNT>
+__device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit &fh, Counters &c, unsigned long long id,
+                                          const int32_t *__restrict__ row_y, unsigned &rays) {
+    const vt_settings &s = P.s;
+    L.st = ST_NONE;
+    const uint32_t packet = (uint32_t)(id >> 5), slot = (uint32_t)id & 31u;
+    uint32_t tile = packet, round = 0;
+    if (P.rounds > 1) { tile = packet / (uint32_t)P.rounds; round = packet - tile * (uint32_t)P.rounds; }
+    const uint32_t pi = slot >> P.group_shift, sample = (slot & (uint32_t)(P.group - 1)) + (uint32_t)P.group * round;
+    int x = 0, y = 0;
+    bool pv;
+    if (P.pixels) {
+        long long i = (long long)tile * (32 >> P.group_shift) + pi;
+        pv = i < P.n_pixels;
+        if (pv) { x = __ldg(P.pixels + 2 * i); y = __ldg(P.pixels + 2 * i + 1); L.out_i = (uint32_t)i; }
+    } else {
+        const int bw = P.x1 - P.x0;
+        uint32_t ty = tile / (uint32_t)P.tiles_x, tx = tile - ty * (uint32_t)P.tiles_x;
+        int lx = pi & (P.tile_w - 1), ly = pi >> P.tile_w_shift;
+        int col = (int)tx * P.tile_w + lx, lr = (int)ty * P.tile_h + ly;
+        pv = col < bw && lr < P.band_rows;
+        if (pv) { x = P.x0 + col; y = __ldg(row_y + lr); L.out_i = (uint32_t)(lr * bw + col); }
+    }
+    if (!pv) return;
+    double dir_x, dir_y, detail;
+    const int n = pixel_samples(P, x, y, dir_x, dir_y, detail);
+    if ((int)sample >= n) return;
+    rays++;
+    L.xy = (uint32_t)x | ((uint32_t)y << 16);
+    L.st = ST_MARCH | (sample << 12);
+    L.draw = 0; L.w2 = L.w3 = 0;
+    double u = lane_rng_next(P, L);                                          // drawn even when lod_random == 0 (init.py:139)
+    double ray_detail = detail / (1.0 + u2d(sample) * s.lod_samples) * (1.0 - s.lod_random * u);
+    double sy, cy, sz, cz;
+    if (s.dof == 0.0 && P.cam.col_sc) {
+        sy = __ldg(P.cam.col_sc + 2 * x); cy = __ldg(P.cam.col_sc + 2 * x + 1);
+        sz = __ldg(P.cam.row_sc + 2 * y); cz = __ldg(P.cam.row_sc + 2 * y + 1);
+    } else {
+        const double deg2rad = 3.14159265358979323846 / 180.0;
+        double lens_x = (dir_x / s.proportions) * P.cam.lens + lane_rng_rand(P, L, s.dof);
+        double lens_y = (dir_y * s.proportions) * P.cam.lens + lane_rng_rand(P, L, s.dof);
+        double rad_y = (-lens_x) * deg2rad, rad_z = (+lens_y) * deg2rad;
+        sincos(rad_y / 2.0, &sy, &cy);
+        sincos(rad_z / 2.0, &sz, &cz);
+    }
+    double dx, dy, dz;
+    ray_dir(P.cam, sy, cy, sz, cz, dx, dy, dz);
+    L.px = P.cam.pos[0] + dx * s.dist_min; L.py = P.cam.pos[1] + dy * s.dist_min; L.pz = P.cam.pos[2] + dz * s.dist_min;
+    L.vx = dx; L.vy = dy; L.vz = dz;
+    L.life = (s.dist_max - s.dist_min) * ray_detail;
+    L.step = 0.0; L.bounces = 0.0; L.energy = 0.0; L.col = 0;
+    L.cx = L.cy = L.cz = 0; L.res = 0;
+    if (REC) { fh.hits = 0; fh.fflag = 0; fh.fx = fh.fy = fh.fz = 0; fh.first_step = -1.0; }
+    if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
+    // The loop starts with chunk_min == chunk_max == (0, 0, 0) and no chunk (init.py:60): a ray that starts
+    // exactly at the world's zero point takes one void step before its first chunk lookup.
+    if (L.px == 0.0 && L.py == 0.0 && L.pz == 0.0) {
+        if (COUNT) c.in_void++;
+        advance(L, void_step2(L.px, L.py, L.pz, s.chunk_radius, s.chunk_size, P.cs_shift));
+        if (lane_state(L) == ST_DONE) return;
+    }
+    int ix = floor_i(L.px) - P.w.ox, iy = floor_i(L.py) - P.w.oy, iz = floor_i(L.pz) - P.w.oz;
+    if (!rechunk<FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
+}
+
+#ifndef VT_MARCH_KEEP
+#define VT_MARCH_KEEP 6             // the march phase goes on while >= KEEP/8 of the lanes that entered it still march
+#endif
+#ifndef VT_MINB
+#define VT_MINB 5                   // resident 128-thread blocks per SM the register budget is sized for
+#endif
+
+// Camera.tile (reference init.py:126-150) for a whole region: one persistent launch.
+template <bool REC, bool FULL_TAIL, bool COUNT>
+__global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_constant__ DevParams P, const int32_t *__restrict__ row_y) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    Lane L;
+    L.st = ST_NONE; L.px = L.py = L.pz = L.vx = L.vy = L.vz = 0.0; L.step = L.life = L.bounces = L.energy = 0.0;
+    L.col = 0; L.cx = L.cy = L.cz = 0; L.res = 0; L.xy = 0; L.out_i = 0; L.draw = L.w2 = L.w3 = 0;
+    FirstHit fh; fh.hits = fh.fflag = fh.fx = fh.fy = fh.fz = 0; fh.first_step = -1.0;
+    Counters c = {0, 0, 0, 0, 0, 0};
+    unsigned rays = 0;
+    bool exhausted = false;                                                  // warp-uniform: the queue is empty
+    for (;;) {
+        const uint32_t state = lane_state(L);
+        const unsigned mM = __ballot_sync(full, state == ST_MARCH), mH = __ballot_sync(full, state == ST_HIT);
+        const unsigned mD = __ballot_sync(full, state == ST_DONE);
+        const int nM = __popc(mM), nH = __popc(mH), nD = __popc(mD);
+        const int nI = exhausted ? nD : 32 - nM - nH;                        // lanes a refill round would serve
+        if (nM + nH == 0 && nI == 0) break;
+        if ((nI >= P.refill_min && nI > nM && nI > nH) || nM + nH == 0) {
+            // ---- refill: finish ended rays, fetch new ray slots --------------------------------------------
+            if (state == ST_DONE) { finish_ray<REC>(P, L, fh); L.st = ST_NONE; }
+            if (!exhausted) {
+                const unsigned need = __ballot_sync(full, lane_state(L) == ST_NONE);
+                const int cnt = __popc(need), leader = __ffs(need) - 1;
+                unsigned long long base = 0;
+                if (lane == leader) base = atomicAdd(P.queue, (unsigned long long)cnt);
+                base = __shfl_sync(full, base, leader);
+                if (lane_state(L) == ST_NONE) {
+                    unsigned long long id = base + (unsigned)__popc(need & ((1u << lane) - 1u));
+                    if (id < P.total_rays) start_ray<REC, FULL_TAIL, COUNT>(P, L, fh, c, id, row_y, rays);
+                }
+                exhausted = base + (unsigned)cnt >= P.total_rays;
+            }
+        } else if (nH > nM) {
+            if (state == ST_HIT) shade_one<REC, COUNT>(P, L, fh, c);
+        } else {
+            // ---- march: iterate until too few lanes are still marching -------------------------------------
+            const int thr = max(1, (nM * VT_MARCH_KEEP) >> 3);
+            for (;;) {
+                int ix = 0, iy = 0, iz = 0, looked = 0;
+                bool leave = false;
+                if (lane_state(L) == ST_MARCH) {
+                    ix = floor_i(L.px) - P.w.ox; iy = floor_i(L.py) - P.w.oy; iz = floor_i(L.pz) - P.w.oz;
+                    const unsigned ux = (unsigned)(ix - L.cx), uy = (unsigned)(iy - L.cy), uz = (unsigned)(iz - L.cz);
+                    leave = max(ux, max(uy, uz)) >= (unsigned)P.s.chunk_size;
+                }
+                if (leave) looked = march_leave_chunk<FULL_TAIL, COUNT>(P, L, c, ix, iy, iz);
+                __syncwarp(full);
+                if (lane_state(L) == ST_MARCH) march_cell<COUNT>(P, L, c, ix, iy, iz, looked);
+                __syncwarp(full);
+                if (__popc(__ballot_sync(full, lane_state(L) == ST_MARCH)) < thr) break;
+            }
+        }
+    }
+    if (COUNT && P.counters) {
+        unsigned v[7] = {rays, c.in_chunk, c.in_void, c.hits, c.probes, c.rechunk, c.in_chunk + c.in_void};
+#pragma unroll
+        for (int k = 0; k < 7; k++) {
+            unsigned t = __reduce_add_sync(full, v[k]);
+            if (lane == 0 && t) atomicAdd(P.counters + k, (unsigned long long)t);
+        }
+    }
+    // the last warp to leave resets the queue for the next launch
+    if (lane == 0) {
+        __threadfence();
+        unsigned long long done = atomicAdd(P.queue + 1, 1ull);
+        if (done == (unsigned long long)P.total_warps - 1ull) { P.queue[0] = 0ull; P.queue[1] = 0ull; }
+    }
+}
+
+}  // namespace vt
