@@ -183,7 +183,8 @@ struct vt_ctx {
     int persist_blocks[4] = {0, 0, 0, 0};                           // resident blocks per SM, per instantiation
     int sm_count = 0;
     int kernel_version = 2;                                         // VT_KERNEL=1 selects the v1 warp-tile kernel (A/B)
-    int refill_min = 8;                                             // VT_REFILL overrides
+    int brick_runs = 1;                                             // VT_RUNS=0 disables empty-brick runs (A/B)
+    int refill_min = 32;                                            // VT_REFILL overrides
     // region row map
     int32_t *d_row_y = nullptr; int row_cap = 0;
     std::vector<int32_t> h_row_y; int row_key[7] = {-1, -1, -1, -1, -1, -1, -1};
@@ -232,6 +233,7 @@ extern "C" int vt_create(int device, vt_ctx **out) {
         return 2;
     }
     if (const char *k = getenv("VT_KERNEL")) ctx->kernel_version = atoi(k) == 1 ? 1 : 2;
+    if (const char *k = getenv("VT_RUNS")) ctx->brick_runs = atoi(k) != 0;
     if (const char *k = getenv("VT_REFILL")) { int v = atoi(k); if (v >= 1 && v <= 32) ctx->refill_min = v; }
     *out = ctx;
     return 0;
@@ -568,6 +570,7 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
         ctx->acc_cap = words;
     }
     P.acc = ctx->d_acc; P.queue = ctx->d_queue; P.refill_min = ctx->refill_min;
+    P.brick_runs = (ctx->brick_runs && s.chunk_size % VT_BRICK == 0) ? 1 : 0;
     for (int r = 2; r <= VT_LOD_TAB; r++) {
         P.lod_magic[r] = (uint32_t)((1ull << 32) / (unsigned)r) + 1u;
         for (int a = 0; a < 3; a++) { int m = ctx->origin[a] % r; P.lod_bias[r][a] = m < 0 ? m + r : m; }

@@ -60,6 +60,7 @@ struct DevParams {
     unsigned long long *queue;      // [0] next ray slot, [1] warps finished; both zero between launches
     unsigned int total_warps;       // warps launched
     int refill_min;                 // refill once this many lanes are idle
+    int brick_runs;                 // 1: chunk_size % 8 == 0, empty-brick runs allowed (VT_RUNS=0 disables, A/B)
     uint32_t lod_magic[VT_LOD_TAB + 1];   // floor(n / r) == umulhi(n, magic[r]) for n < 2^24 / r ... (r >= 2)
     int32_t lod_bias[VT_LOD_TAB + 1][3];  // world origin mod r per axis
     // outputs

@@ -59,6 +59,12 @@ __device__ __forceinline__ double lane_rng_rand(const DevParams &P, Lane &L, dou
     return (-1.0 + lane_rng_next(P, L) * 2.0) * amp;
 }
 
+// Integer divisions by run-time divisors (chunk sizes that are not powers of two, resolutions above the snap table)
+// live in functions that are never inlined: inlined, ptxas if-converts the rare branch and every sample pays for a
+// 20-instruction division it does not use.
+__device__ __noinline__ int floordiv_mul_slow(int a, int b) { return ifloordiv(a, b) * b; }
+__device__ __noinline__ int div_slow(int a, int b) { return a / b; }
+
 // ---- cell addressing, relative to the world origin ------------------------------------------------------------
 // res * floor(abs / res) - origin for abs = r + origin, r >= 0 (data.py:137 with Python's floor division)
 __device__ __forceinline__ int lod_snap(const DevParams &P, int res, int r, int axis) {
@@ -68,7 +74,7 @@ __device__ __forceinline__ int lod_snap(const DevParams &P, int res, int r, int 
         return (int)(f * (uint32_t)res) - b;
     }
     int o = axis == 0 ? P.w.ox : axis == 1 ? P.w.oy : P.w.oz;
-    return ifloordiv(r + o, res) * res - o;
+    return floordiv_mul_slow(r + o, res) - o;
 }
 
 __device__ __forceinline__ int cell_at(const DevWorld &w, int qx, int qy, int qz) {
@@ -89,7 +95,8 @@ __device__ __forceinline__ int lookup_any(const DevParams &P, int cx, int cy, in
 }
 
 __device__ __forceinline__ int snap_rel(int r, int cs, int cs_shift) {   // origin is a multiple of chunk_size
-    return cs_shift >= 0 ? ((r >> cs_shift) << cs_shift) : ifloordiv(r, cs) * cs;
+    if (cs_shift >= 0) return (r >> cs_shift) << cs_shift;
+    return floordiv_mul_slow(r, cs);
 }
 
 // chunk slot of the chunk at relative origin (cx, cy, cz), or -1 (`post in self.chunks` is false outside the box)
@@ -97,7 +104,7 @@ __device__ __forceinline__ int chunk_slot_rel(const DevWorld &w, int cs, int cs_
     if ((unsigned)cx >= (unsigned)w.nx || (unsigned)cy >= (unsigned)w.ny || (unsigned)cz >= (unsigned)w.nz) return -1;
     int sx, sy, sz;
     if (cs_shift >= 0) { sx = cx >> cs_shift; sy = cy >> cs_shift; sz = cz >> cs_shift; }
-    else { sx = cx / cs; sy = cy / cs; sz = cz / cs; }
+    else { sx = div_slow(cx, cs); sy = div_slow(cy, cs); sz = div_slow(cz, cs); }
     return (sx * w.ncy + sy) * w.ncz + sz;
 }
 
@@ -160,29 +167,52 @@ __device__ __forceinline__ int march_leave_chunk(const DevParams &P, Lane &L, Co
 
 // Block B (init.py:75-77, 114-116): examine the cell under the ray; a solid one turns the lane into HIT (the position
 // is not advanced -- the material phase does that), an empty one advances the ray.
+//
+// Empty-brick run: when the cell's 8^3 brick holds no voxel at all, every further sample that still falls into the
+// same brick is known to be empty and inside the same chunk (bricks never straddle chunks when chunk_size % 8 == 0),
+// so those samples only need the position update and the floor -- the sample positions themselves are the
+// reference's, one fp64 add per axis per sample.  This is what shortens the long rays of a packet.
 template <bool COUNT>
 __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters &c, int ix, int iy, int iz, int looked) {
     const DevWorld &w = P.w;
-    double step;
     if (L.res) {
         if (COUNT) c.in_chunk++;
         int mat = looked - 1;
         if (!looked) {
+            mat = 0;
             int qx = ix, qy = iy, qz = iz;
             bool in = true;
             if (L.res > 1) {
                 qx = lod_snap(P, L.res, ix, 0); qy = lod_snap(P, L.res, iy, 1); qz = lod_snap(P, L.res, iz, 2);
                 in = qx >= L.cx && qy >= L.cy && qz >= L.cz;            // q <= i, so only the near faces can fail
             }
-            mat = in ? cell_at(w, qx, qy, qz) : 0;
+            if (in) {
+                const uint32_t b = __ldg(&w.brick_tab[((qx >> 3) * w.nby + (qy >> 3)) * w.nbz + (qz >> 3)]);
+                if (b) mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
+                else if (L.res == 1 && P.brick_runs) {
+                    for (;;) {
+                        L.step += 1.0;
+                        L.px += L.vx; L.py += L.vy; L.pz += L.vz;       // vel * 1.0 == vel
+                        if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
+                        const int jx = floor_i(L.px) - w.ox, jy = floor_i(L.py) - w.oy, jz = floor_i(L.pz) - w.oz;
+                        if ((((jx ^ ix) | (jy ^ iy) | (jz ^ iz)) & ~7) != 0) return;      // next sample: another brick
+                        if (COUNT) c.in_chunk++;
+                    }
+                }
+            }
         }
         if (mat) { L.st = (L.st & ~0xfffu) | ST_HIT | ((uint32_t)mat << 2); return; }
-        step = i2d(L.res);
+        if (L.res == 1) {
+            L.step += 1.0;
+            L.px += L.vx; L.py += L.vy; L.pz += L.vz;
+            if (!(L.step < L.life)) lane_set_state(L, ST_DONE);
+            return;
+        }
+        advance(L, i2d(L.res));
     } else {
         if (COUNT) c.in_void++;
-        step = void_step2(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift);
+        advance(L, void_step2(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift));
     }
-    advance(L, step);
 }
 
 // lib.material (lib.py:448-460) + the post-hit part of the loop body (init.py:78-116) for a HIT lane.
@@ -407,10 +437,10 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
 }
 
 #ifndef VT_MARCH_KEEP
-#define VT_MARCH_KEEP 6             // the march phase goes on while >= KEEP/8 of the lanes that entered it still march
+#define VT_MARCH_KEEP 1             // the march phase goes on while >= KEEP/8 of the lanes that entered it still march
 #endif
 #ifndef VT_MINB
-#define VT_MINB 5                   // resident 128-thread blocks per SM the register budget is sized for
+#define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
 #endif
 
 // Camera.tile (reference init.py:126-150) for a whole region: one persistent launch.
