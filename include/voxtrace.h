@@ -85,6 +85,32 @@ int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells);
 /* Bytes of device memory held by bricks / number of non-empty bricks (reporting). */
 int vt_world_stats(vt_ctx *ctx, int64_t *n_bricks, int64_t *bytes);
 
+/* ---- scene building: what Window.chunk_update does before the path (init.py:389-452) ------------------------- */
+/* One world object as chunk_update sees it: the active frame of its sprite as a dense grid of material ids
+ * (Sprite.get_voxel -> Frame.get_voxel, data.py:417-419, 136-145; sprites of resolution 1), its integer box
+ * (Object.mins / maxs, data.py:480-484, 592-594) and its 90-degree rotation steps round(rot / 90) % 4
+ * (Sprite.pos_rotated, data.py:338-371). */
+typedef struct {
+    const uint8_t *dev_sprite;     /* [size0][size1][size2] u8, z fastest; 0 = no voxel */
+    int32_t size[3];               /* Sprite.size */
+    int32_t mins[3], maxs[3];      /* cells mins <= p < maxs are drawn (init.py:413-419) */
+    int32_t angle[3];              /* 0..3 per axis */
+    int32_t reserved;
+} vt_object;
+/* Draws n objects into a dense [dims0][dims1][dims2] u8 grid in DEVICE memory covering the box of vt_set_world:
+ * cell = material of the LAST object in the list that has a voxel there (chunk frames are merged in object order,
+ * later ones override, init.py:437-439).  Follow with vt_upload_dense(ctx, dev_cells).  One kernel launch. */
+int vt_build_world(vt_ctx *ctx, const vt_object *host_objects, int n, uint8_t *dev_cells);
+
+/* Goxel text model -> voxel list, the parser rules of Sprite.load (data.py:271-289): single-space separated
+ * "x y z rrggbb" lines, non-numeric lines skipped, colours looked up in `keys` (n_keys strings; unknown ones are
+ * dropped), position (size_x - x, z, y).  Returns malloc'ed arrays in FILE ORDER (later entries override earlier
+ * ones): out_xyz [n][3] int32, out_mat [n] u8 = index into keys + 1.  Release both with vt_free.  `.txt` is
+ * mmap'ed, `.gz` goes through zlib.  Pure host code (no context, no GPU). */
+int vt_goxel_parse(const char *path, int32_t size_x, const char *const *keys, int n_keys, int32_t **out_xyz,
+                   uint8_t **out_mat, int64_t *out_n, char *err, int err_len);
+void vt_free(void *p);
+
 /* ---- render: Camera.tile (init.py:126-150) --------------------------------------------------------- */
 /* Pixel set of one call.  The reference hands each worker `settings.pixels[thread]` (data.py:70-77); here a
  * call covers either a rectangle of interleaved row stripes or an explicit pixel list:

@@ -14,7 +14,7 @@ RAY_RECORD = 16
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
            "vt_set_settings", "vt_set_materials", "vt_set_camera", "vt_set_world", "vt_set_chunk_table",
            "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
-           "vt_launch_count")
+           "vt_launch_count", "vt_build_world", "vt_goxel_parse", "vt_free")
 
 
 class VtSettings(C.Structure):
@@ -30,6 +30,11 @@ class VtRegion(C.Structure):
     _fields_ = [("x0", C.c_int32), ("y0", C.c_int32), ("x1", C.c_int32), ("y1", C.c_int32),
                 ("stripe_rows", C.c_int32), ("stripe_count", C.c_int32), ("stripe_index", C.c_int32),
                 ("reserved", C.c_int32), ("dev_pixels", C.c_void_p), ("n_pixels", C.c_int64)]
+
+
+class VtObject(C.Structure):
+    _fields_ = [("dev_sprite", C.c_void_p), ("size", C.c_int32 * 3), ("mins", C.c_int32 * 3), ("maxs", C.c_int32 * 3),
+                ("angle", C.c_int32 * 3), ("reserved", C.c_int32)]
 
 
 class VoxtraceError(RuntimeError):
@@ -70,6 +75,10 @@ def load(path: str | None = None):
         "vt_render": (C.c_int, [vp, C.POINTER(VtRegion), vp, vp, vp, vp, vp, u64]),
         "vt_region_pixels": (i64, [C.POINTER(VtRegion)]),
         "vt_launch_count": (i64, [vp]),
+        "vt_build_world": (C.c_int, [vp, C.POINTER(VtObject), i32, vp]),
+        "vt_goxel_parse": (C.c_int, [C.c_char_p, C.c_int32, C.POINTER(C.c_char_p), i32, C.POINTER(C.POINTER(C.c_int32)),
+                                     C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(i64), C.c_char_p, i32]),
+        "vt_free": (None, [vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

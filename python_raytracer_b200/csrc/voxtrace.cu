@@ -146,6 +146,45 @@ __global__ void brick_fill_kernel(const uint8_t *__restrict__ dense, int nx, int
     }
 }
 
+// Sprite.pos_rotated (reference data.py:338-371): 90-degree steps, each axis only when the two other sizes match
+__device__ __forceinline__ void pos_rotated(const vt_object &o, int &x, int &y, int &z) {
+    const int ex = o.size[0] - 1, ey = o.size[1] - 1, ez = o.size[2] - 1;
+    int ax = o.angle[0], ay = o.angle[1], az = o.angle[2], nx, ny, nz;
+    if (ax && o.size[1] == o.size[2]) {
+        if (ax == 1) { ny = ez - z; nz = y; } else if (ax == 2) { ny = ey - y; nz = ez - z; } else { ny = z; nz = ey - y; }
+        y = ny; z = nz;
+    }
+    if (ay && o.size[0] == o.size[2]) {
+        if (ay == 1) { nx = z; nz = ex - x; } else if (ay == 2) { nx = ex - x; nz = ez - z; } else { nx = ez - z; nz = x; }
+        x = nx; z = nz;
+    }
+    if (az && o.size[0] == o.size[1]) {
+        if (az == 1) { nx = ey - y; ny = x; } else if (az == 2) { nx = ex - x; ny = ey - y; } else { nx = y; ny = ex - x; }
+        x = nx; y = ny;
+    }
+}
+
+// Window.chunk_update's voxel gathering (init.py:413-424, 437-439) as one pass over the world's cells: the last
+// object in list order that has a voxel at the cell wins.
+__global__ void build_world_kernel(const vt_object *__restrict__ objs, int n, int ox, int oy, int oz, int nx, int ny, int nz,
+                                   uint8_t *__restrict__ cells) {
+    const long long total = (long long)nx * ny * nz;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        int z = (int)(i % nz), y = (int)((i / nz) % ny), x = (int)(i / ((long long)nz * ny));
+        const int wx = x + ox, wy = y + oy, wz = z + oz;
+        uint8_t m = 0;
+        for (int k = n - 1; k >= 0 && !m; k--) {
+            const vt_object &o = objs[k];
+            if (wx < o.mins[0] || wx >= o.maxs[0] || wy < o.mins[1] || wy >= o.maxs[1] || wz < o.mins[2] || wz >= o.maxs[2]) continue;
+            int lx = wx - o.mins[0], ly = wy - o.mins[1], lz = wz - o.mins[2];
+            pos_rotated(o, lx, ly, lz);
+            if ((unsigned)lx >= (unsigned)o.size[0] || (unsigned)ly >= (unsigned)o.size[1] || (unsigned)lz >= (unsigned)o.size[2]) continue;
+            m = o.dev_sprite[((size_t)lx * o.size[1] + ly) * o.size[2] + lz];
+        }
+        cells[i] = m;
+    }
+}
+
 // ------------------------------------------------------------------------------------------------------
 // host side: context + C ABI
 
@@ -441,6 +480,34 @@ extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
         VT_CHECK(ctx, cudaGetLastError());
     }
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+
+extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t *dev_cells) {
+    if (!ctx || !dev_cells || n < 0 || (n && !objs)) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_build_world: no world (vt_set_world)");
+    for (int k = 0; k < n; k++) {
+        if (!objs[k].dev_sprite) return fail(ctx, "vt_build_world: object without a sprite grid");
+        for (int a = 0; a < 3; a++) {
+            if (objs[k].size[a] <= 0) return fail(ctx, "vt_build_world: sprite size must be positive");
+            if (objs[k].angle[a] < 0 || objs[k].angle[a] > 3) return fail(ctx, "vt_build_world: angle must be 0..3");
+        }
+    }
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    vt_object *d_objs = nullptr;
+    if (n) {
+        VT_CHECK(ctx, cudaMalloc(&d_objs, (size_t)n * sizeof(vt_object)));
+        VT_CHECK(ctx, cudaMemcpyAsync(d_objs, objs, (size_t)n * sizeof(vt_object), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ctx->dims[2];
+    long long want = (total + 255) / 256;
+    int grid = (int)(want < 148LL * 32 ? want : 148LL * 32);
+    build_world_kernel<<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[0],
+                                                      ctx->dims[1], ctx->dims[2], dev_cells);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_objs);
     return 0;
 }
 
