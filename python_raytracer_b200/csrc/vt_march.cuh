@@ -42,15 +42,29 @@ __device__ __forceinline__ uint32_t lane_state(const Lane &L) { return L.st & 3u
 __device__ __forceinline__ uint32_t lane_sample(const Lane &L) { return L.st >> 12; }
 __device__ __forceinline__ void lane_set_state(Lane &L, uint32_t s) { L.st = (L.st & ~0xffcu & ~3u) | s; }
 
+// Out-of-line helpers: each is called from several places and is long (Philox 80 instructions, sincos and pow with
+// their argument-reduction paths); inlined copies made the kernel 25 % larger and it is sensitive to instruction-cache
+// misses (profiles/r1_v2b: no_instruction is the largest stall reason).
+__device__ __noinline__ uint4 philox_block(uint32_t block, uint32_t sample, uint32_t seed_lo, uint32_t seed_hi, uint32_t pix) {
+    uint32_t w[4];
+    philox4x32_10(block, sample, seed_lo, seed_hi, pix, 0u, w);
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __noinline__ double2 sincos_out(double a) {
+    double s, c;
+    sincos(a, &s, &c);
+    return make_double2(s, c);
+}
+__device__ __noinline__ double pow_out(double a, double b) { return pow(a, b); }
+
 // ---- Philox stream of one ray: key = global pixel index, counter = (block, sample, frame seed) --------------
 __device__ __forceinline__ double lane_rng_next(const DevParams &P, Lane &L) {
     uint32_t d = L.draw++;
     if ((d & 1u) == 0u) {
-        uint32_t w[4];
         uint32_t pix = (L.xy >> 16) * (uint32_t)P.s.width + (L.xy & 0xffffu);
-        philox4x32_10(d >> 1, lane_sample(L), P.seed_lo, P.seed_hi, pix, 0u, w);
-        L.w2 = w[2]; L.w3 = w[3];
-        return u53m(w[0], w[1]);
+        uint4 w = philox_block(d >> 1, lane_sample(L), P.seed_lo, P.seed_hi, pix);
+        L.w2 = w.z; L.w3 = w.w;
+        return u53m(w.x, w.y);
     }
     return u53m(L.w2, L.w3);
 }
@@ -67,8 +81,9 @@ __device__ __noinline__ int div_slow(int a, int b) { return a / b; }
 
 // ---- cell addressing, relative to the world origin ------------------------------------------------------------
 // res * floor(abs / res) - origin for abs = r + origin, r >= 0 (data.py:137 with Python's floor division)
+template <bool FAST>
 __device__ __forceinline__ int lod_snap(const DevParams &P, int res, int r, int axis) {
-    if (res <= VT_LOD_TAB) {
+    if (FAST || res <= VT_LOD_TAB) {
         int b = P.lod_bias[res][axis];
         uint32_t f = __umulhi((uint32_t)(r + b), P.lod_magic[res]);
         return (int)(f * (uint32_t)res) - b;
@@ -85,37 +100,40 @@ __device__ __forceinline__ int cell_at(const DevWorld &w, int qx, int qy, int qz
 
 // Frame.get_voxel (data.py:136-145) of the LOD-`res` frame of the chunk at (cx, cy, cz) for ANY cell (jx, jy, jz):
 // the key floor(p) // res exists iff the cell res * key lies inside that chunk (init.py:417-424, data.py:165-169).
+template <bool FAST>
 __device__ __forceinline__ int lookup_any(const DevParams &P, int cx, int cy, int cz, int res, int jx, int jy, int jz) {
     const int cs = P.s.chunk_size;
     if ((jx | jy | jz) < 0) return 0;                  // below the world box: res * key <= j is outside too
-    if (res > 1) { jx = lod_snap(P, res, jx, 0); jy = lod_snap(P, res, jy, 1); jz = lod_snap(P, res, jz, 2); }
+    if (res > 1) { jx = lod_snap<FAST>(P, res, jx, 0); jy = lod_snap<FAST>(P, res, jy, 1); jz = lod_snap<FAST>(P, res, jz, 2); }
     if ((unsigned)(jx - cx) >= (unsigned)cs || (unsigned)(jy - cy) >= (unsigned)cs || (unsigned)(jz - cz) >= (unsigned)cs)
         return 0;
     return cell_at(P.w, jx, jy, jz);
 }
 
+template <bool FAST>
 __device__ __forceinline__ int snap_rel(int r, int cs, int cs_shift) {   // origin is a multiple of chunk_size
-    if (cs_shift >= 0) return (r >> cs_shift) << cs_shift;
+    if (FAST || cs_shift >= 0) return (r >> cs_shift) << cs_shift;
     return floordiv_mul_slow(r, cs);
 }
 
 // chunk slot of the chunk at relative origin (cx, cy, cz), or -1 (`post in self.chunks` is false outside the box)
+template <bool FAST>
 __device__ __forceinline__ int chunk_slot_rel(const DevWorld &w, int cs, int cs_shift, int cx, int cy, int cz) {
     if ((unsigned)cx >= (unsigned)w.nx || (unsigned)cy >= (unsigned)w.ny || (unsigned)cz >= (unsigned)w.nz) return -1;
     int sx, sy, sz;
-    if (cs_shift >= 0) { sx = cx >> cs_shift; sy = cy >> cs_shift; sz = cz >> cs_shift; }
+    if (FAST || cs_shift >= 0) { sx = cx >> cs_shift; sy = cy >> cs_shift; sz = cz >> cs_shift; }
     else { sx = div_slow(cx, cs); sy = div_slow(cy, cs); sz = div_slow(cz, cs); }
     return (sx * w.ncy + sy) * w.ncz + sz;
 }
 
 // init.py:67-73: re-snap the chunk box around the cell (ix, iy, iz), look the chunk up, record it as traversed.
 // Returns false when the ray can stop (FULL_TAIL == false): outside the world box and moving away from it.
-template <bool FULL_TAIL, bool COUNT>
+template <bool FAST, bool FULL_TAIL, bool COUNT>
 __device__ __forceinline__ bool rechunk(const DevParams &P, Lane &L, int ix, int iy, int iz, Counters &c) {
     const DevWorld &w = P.w;
     const int cs = P.s.chunk_size, sh = P.cs_shift;
-    L.cx = snap_rel(ix, cs, sh); L.cy = snap_rel(iy, cs, sh); L.cz = snap_rel(iz, cs, sh);
-    int slot = chunk_slot_rel(w, cs, sh, L.cx, L.cy, L.cz);
+    L.cx = snap_rel<FAST>(ix, cs, sh); L.cy = snap_rel<FAST>(iy, cs, sh); L.cz = snap_rel<FAST>(iz, cs, sh);
+    int slot = chunk_slot_rel<FAST>(w, cs, sh, L.cx, L.cy, L.cz);
     L.res = 0;
     if (COUNT) c.rechunk++;
     if (slot >= 0) { L.res = __ldg(&w.chunk_res[slot]); mark_visited(P.visited, slot); }
@@ -128,10 +146,11 @@ __device__ __forceinline__ bool rechunk(const DevParams &P, Lane &L, int ix, int
 }
 
 // void step of init.py:114 (see vt_device.cuh void_step); for a power-of-two chunk size a / cs == a * (1 / cs) exactly
+template <bool FAST>
 __device__ __forceinline__ double void_step2(double px, double py, double pz, int radius, int cs, int cs_shift) {
     double a = fmin(px, fmin(py, pz)) + i2d(radius);
     double m;
-    if (cs_shift >= 0) {
+    if (FAST || cs_shift >= 0) {
         double dcs = i2d(cs), inv = __hiloint2double((1023 - cs_shift) << 20, 0);
         m = a - dcs * floor_d(a * inv);
     } else m = py_mod_pos(a, i2d(cs));
@@ -152,7 +171,7 @@ __device__ __forceinline__ void advance(Lane &L, double step) {          // init
 // inclusive at chunk_max (lib.py:228-244): a position exactly on the far face(s) stays in the old chunk ("sticky");
 // then the cell is looked up with the old chunk's frame right here and `mat` carries the answer to block B as
 // mat + 1 (0 = not looked up yet).
-template <bool FULL_TAIL, bool COUNT>
+template <bool FAST, bool FULL_TAIL, bool COUNT>
 __device__ __forceinline__ int march_leave_chunk(const DevParams &P, Lane &L, Counters &c, int ix, int iy, int iz) {
     const DevWorld &w = P.w;
     const unsigned cs = (unsigned)P.s.chunk_size;
@@ -160,8 +179,8 @@ __device__ __forceinline__ int march_leave_chunk(const DevParams &P, Lane &L, Co
     bool sticky = false;
     if (max(ux, max(uy, uz)) == cs)
         sticky = (ux < cs || L.px == i2d(ix + w.ox)) && (uy < cs || L.py == i2d(iy + w.oy)) && (uz < cs || L.pz == i2d(iz + w.oz));
-    if (sticky) return 1 + (L.res ? lookup_any(P, L.cx, L.cy, L.cz, L.res, ix, iy, iz) : 0);
-    if (!rechunk<FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
+    if (sticky) return 1 + (L.res ? lookup_any<FAST>(P, L.cx, L.cy, L.cz, L.res, ix, iy, iz) : 0);
+    if (!rechunk<FAST, FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
     return 0;
 }
 
@@ -172,7 +191,7 @@ __device__ __forceinline__ int march_leave_chunk(const DevParams &P, Lane &L, Co
 // same brick is known to be empty and inside the same chunk (bricks never straddle chunks when chunk_size % 8 == 0),
 // so those samples only need the position update and the floor -- the sample positions themselves are the
 // reference's, one fp64 add per axis per sample.  This is what shortens the long rays of a packet.
-template <bool COUNT>
+template <bool FAST, bool COUNT>
 __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters &c, int ix, int iy, int iz, int looked) {
     const DevWorld &w = P.w;
     if (L.res) {
@@ -183,7 +202,7 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
             int qx = ix, qy = iy, qz = iz;
             bool in = true;
             if (L.res > 1) {
-                qx = lod_snap(P, L.res, ix, 0); qy = lod_snap(P, L.res, iy, 1); qz = lod_snap(P, L.res, iz, 2);
+                qx = lod_snap<FAST>(P, L.res, ix, 0); qy = lod_snap<FAST>(P, L.res, iy, 1); qz = lod_snap<FAST>(P, L.res, iz, 2);
                 in = qx >= L.cx && qy >= L.cy && qz >= L.cz;            // q <= i, so only the near faces can fail
             }
             if (in) {
@@ -211,12 +230,12 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
         advance(L, i2d(L.res));
     } else {
         if (COUNT) c.in_void++;
-        advance(L, void_step2(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift));
+        advance(L, void_step2<FAST>(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift));
     }
 }
 
 // lib.material (lib.py:448-460) + the post-hit part of the loop body (init.py:78-116) for a HIT lane.
-template <bool REC, bool COUNT>
+template <bool FAST, bool REC, bool COUNT>
 __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit &fh, Counters &c) {
     const vt_settings &s = P.s;
     const DevWorld &w = P.w;
@@ -233,7 +252,7 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
     double alb_r = __ldg(m + 0), alb_g = __ldg(m + 1), alb_b = __ldg(m + 2);
     double rough = __ldg(m + 3), absorb = __ldg(m + 4), emit = __ldg(m + 6);
     // pow(1, y) == 1 exactly: the first interaction of a ray (bounces == 0) needs no pow
-    double pw = (L.bounces == 0.0) ? 1.0 : pow(1.0 + L.bounces, 1.0 + s.falloff);
+    double pw = (L.bounces == 0.0) ? 1.0 : pow_out(1.0 + L.bounces, 1.0 + s.falloff);
     double a = fmin(1.0, absorb / pw);
     double b2 = 1.0 - a;
     int cr = rint_i(i2d(L.col & 255) * b2 + alb_r * a);
@@ -270,13 +289,13 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
             int nid = 0;
             // `pos >= chunk_min and pos <= chunk_max` on the probed axis (the other two are the hit cell's own)
             if (u < (unsigned)cs || (u == (unsigned)cs && qa == i2d(ja + oa))) {
-                nid = lookup_any(P, L.cx, L.cy, L.cz, L.res, jx_, jy_, jz_);
+                nid = lookup_any<FAST>(P, L.cx, L.cy, L.cz, L.res, jx_, jy_, jz_);
                 if (COUNT) c.probes++;
             } else {                                                         // Camera.chunk_get, init.py:28-33
-                int nx = snap_rel(jx_, cs, sh), ny = snap_rel(jy_, cs, sh), nz = snap_rel(jz_, cs, sh);
-                int nslot = chunk_slot_rel(w, cs, sh, nx, ny, nz);
+                int nx = snap_rel<FAST>(jx_, cs, sh), ny = snap_rel<FAST>(jy_, cs, sh), nz = snap_rel<FAST>(jz_, cs, sh);
+                int nslot = chunk_slot_rel<FAST>(w, cs, sh, nx, ny, nz);
                 int nres = nslot >= 0 ? (int)__ldg(&w.chunk_res[nslot]) : 0;
-                if (nres) { nid = lookup_any(P, nx, ny, nz, nres, jx_, jy_, jz_); if (COUNT) c.probes++; }
+                if (nres) { nid = lookup_any<FAST>(P, nx, ny, nz, nres, jx_, jy_, jz_); if (COUNT) c.probes++; }
             }
             flip[k] = (nid == 0) || (__ldg(w.mats + 8 * nid + 5) != ior);
         }
@@ -301,12 +320,12 @@ __device__ __forceinline__ int pixel_samples(const DevParams &P, int x, int y, d
 
 // End of a ray (init.py:119-121, 141-146): background, alpha, then add the sample to its pixel.  The sample that
 // completes the pixel computes the mean (lib.average, lib.py:419-428), writes it and clears the accumulator.
-template <bool REC>
+template <bool FAST, bool REC>
 __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const FirstHit &fh) {
     const vt_settings &s = P.s;
     double cr = i2d(L.col & 255), cg = i2d((L.col >> 8) & 255), cb = i2d((L.col >> 16) & 255);
     if (s.background) {                                                      // lib.material_background, lib.py:463-476
-        double pw = (L.bounces == 0.0) ? 1.0 : pow(1.0 + L.bounces, 1.0 + s.falloff);
+        double pw = (L.bounces == 0.0) ? 1.0 : pow_out(1.0 + L.bounces, 1.0 + s.falloff);
         double a = fmin(1.0, 1.0 / pw);
         double up = fmax(0.0, L.vy);
         double b2 = 1.0 - a;
@@ -335,7 +354,7 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
     unsigned long long ub = (unsigned)rint_i(fmax(cb, 0.0)), ua = (unsigned)rint_i(fmax(alpha, 0.0));
     unsigned long long sr, sg, sb, sa;
     bool last;
-    if (!P.acc_wide) {
+    if (FAST || !P.acc_wide) {
         unsigned long long add = ur | (ug << 14) | (ub << 28) | (ua << 42) | (1ull << 56);
         unsigned long long tot = atomicAdd(P.acc + i, add) + add;
         last = (int)(tot >> 56) == n;
@@ -371,7 +390,7 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
 
 // Start of a ray (init.py:131-139, 41-59) for ray slot `id`.  Slots enumerate (pixel tile, sample round, lane):
 // 32 consecutive slots are the G samples of 32/G neighbouring pixels, so lanes refilled together start coherent.
-template <bool REC, bool FULL_TAIL, bool COUNT>
+template <bool FAST, bool REC, bool FULL_TAIL, bool COUNT>
 __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit &fh, Counters &c, unsigned long long id,
                                           const int32_t *__restrict__ row_y, unsigned &rays) {
     const vt_settings &s = P.s;
@@ -413,8 +432,8 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
         double lens_x = (dir_x / s.proportions) * P.cam.lens + lane_rng_rand(P, L, s.dof);
         double lens_y = (dir_y * s.proportions) * P.cam.lens + lane_rng_rand(P, L, s.dof);
         double rad_y = (-lens_x) * deg2rad, rad_z = (+lens_y) * deg2rad;
-        sincos(rad_y / 2.0, &sy, &cy);
-        sincos(rad_z / 2.0, &sz, &cz);
+        double2 scy = sincos_out(rad_y / 2.0), scz = sincos_out(rad_z / 2.0);
+        sy = scy.x; cy = scy.y; sz = scz.x; cz = scz.y;
     }
     double dx, dy, dz;
     ray_dir(P.cam, sy, cy, sz, cz, dx, dy, dz);
@@ -429,11 +448,11 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
     // exactly at the world's zero point takes one void step before its first chunk lookup.
     if (L.px == 0.0 && L.py == 0.0 && L.pz == 0.0) {
         if (COUNT) c.in_void++;
-        advance(L, void_step2(L.px, L.py, L.pz, s.chunk_radius, s.chunk_size, P.cs_shift));
+        advance(L, void_step2<FAST>(L.px, L.py, L.pz, s.chunk_radius, s.chunk_size, P.cs_shift));
         if (lane_state(L) == ST_DONE) return;
     }
     int ix = floor_i(L.px) - P.w.ox, iy = floor_i(L.py) - P.w.oy, iz = floor_i(L.pz) - P.w.oz;
-    if (!rechunk<FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
+    if (!rechunk<FAST, FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
 }
 
 #ifndef VT_MARCH_KEEP
@@ -444,7 +463,7 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
 #endif
 
 // Camera.tile (reference init.py:126-150) for a whole region: one persistent launch.
-template <bool REC, bool FULL_TAIL, bool COUNT>
+template <bool FAST, bool REC, bool FULL_TAIL, bool COUNT>
 __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_constant__ DevParams P, const int32_t *__restrict__ row_y) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
@@ -464,7 +483,7 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
         if (nM + nH == 0 && nI == 0) break;
         if ((nI >= P.refill_min && nI > nM && nI > nH) || nM + nH == 0) {
             // ---- refill: finish ended rays, fetch new ray slots --------------------------------------------
-            if (state == ST_DONE) { finish_ray<REC>(P, L, fh); L.st = ST_NONE; }
+            if (state == ST_DONE) { finish_ray<FAST, REC>(P, L, fh); L.st = ST_NONE; }
             if (!exhausted) {
                 const unsigned need = __ballot_sync(full, lane_state(L) == ST_NONE);
                 const int cnt = __popc(need), leader = __ffs(need) - 1;
@@ -473,12 +492,12 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
                 base = __shfl_sync(full, base, leader);
                 if (lane_state(L) == ST_NONE) {
                     unsigned long long id = base + (unsigned)__popc(need & ((1u << lane) - 1u));
-                    if (id < P.total_rays) start_ray<REC, FULL_TAIL, COUNT>(P, L, fh, c, id, row_y, rays);
+                    if (id < P.total_rays) start_ray<FAST, REC, FULL_TAIL, COUNT>(P, L, fh, c, id, row_y, rays);
                 }
                 exhausted = base + (unsigned)cnt >= P.total_rays;
             }
         } else if (nH > nM) {
-            if (state == ST_HIT) shade_one<REC, COUNT>(P, L, fh, c);
+            if (state == ST_HIT) shade_one<FAST, REC, COUNT>(P, L, fh, c);
         } else {
             // ---- march: iterate until too few lanes are still marching -------------------------------------
             const int thr = max(1, (nM * VT_MARCH_KEEP) >> 3);
@@ -490,9 +509,9 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
                     const unsigned ux = (unsigned)(ix - L.cx), uy = (unsigned)(iy - L.cy), uz = (unsigned)(iz - L.cz);
                     leave = max(ux, max(uy, uz)) >= (unsigned)P.s.chunk_size;
                 }
-                if (leave) looked = march_leave_chunk<FULL_TAIL, COUNT>(P, L, c, ix, iy, iz);
+                if (leave) looked = march_leave_chunk<FAST, FULL_TAIL, COUNT>(P, L, c, ix, iy, iz);
                 __syncwarp(full);
-                if (lane_state(L) == ST_MARCH) march_cell<COUNT>(P, L, c, ix, iy, iz, looked);
+                if (lane_state(L) == ST_MARCH) march_cell<FAST, COUNT>(P, L, c, ix, iy, iz, looked);
                 __syncwarp(full);
                 if (__popc(__ballot_sync(full, lane_state(L) == ST_MARCH)) < thr) break;
             }
