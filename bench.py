@@ -58,7 +58,7 @@ class ClockSampler:
         self.lines, self.proc = [], None
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._pump, daemon=True)
             self.t.start()
@@ -248,10 +248,16 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
+    traffic, traffic_src = None, None
+    try:          # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+        traffic, traffic_src = float(tj["traffic_bytes_per_launch_mean"]), tj["source"]
+    except Exception:
+        pass
     achieved = alg_bytes / (t_kernel * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                "traffic": None, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
-                "kernel": "render_kernel", "kernel_ms_per_launch": t_kernel / args.steps,
+                "traffic": traffic, "traffic_source": traffic_src, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
+                "kernel": "render_persistent", "kernel_ms_per_launch": t_kernel / args.steps,
                 "alg_bytes_per_launch": alg_bytes / args.steps,
                 "per_ray": {k: float(cnt_tot[j]) / max(1, cnt_tot[0]) for j, k in
                             enumerate(["rays", "in_chunk_samples", "void_samples", "hits", "neighbour_probes", "chunk_reevals", "iterations"])}}
@@ -280,8 +286,8 @@ def BUILTIN_BG(ray, settings):   # identity token for "data.background is lib.ma
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
