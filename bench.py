@@ -129,19 +129,21 @@ def run_reference(args, rank, world):
     line = {"metric": METRIC, "value": v, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1000.0 * secs / args.steps, "ms_per_full_frame_est": 1000.0 * frame_rays / v,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": workload_config(1, sample="every %dth pixel in x and y" % stride),
+            "config": workload_config(1, False, sample="every %dth pixel in x and y" % stride),
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                              "sample": "each step = every %dth pixel in x and y of one 1920x1080x4spp frame (%d rays)" % (stride, rays_step)},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 
 
-def workload_config(n_gpus, **extra):
+def workload_config(n_gpus, peer=False, **extra):
     c = {"workload": "default mod scene (castle + 6 material cubes + player), 1920x1080, samples=4, max_bounces=4, "
                      "dof=0.5, lod_random=0.25, lod_edge=0, shipped rough/glass/mist materials, 4 camera poses cycled "
                      "(BASELINE.json configs[2])",
          "rays_per_frame": C3_SETTINGS["width"] * C3_SETTINGS["height"] * C3_SETTINGS["samples"],
-         "parallelism": "image split in interleaved 8-row stripes over %d GPU(s), scene replicated, NCCL gather to rank 0" % n_gpus,
+         "parallelism": "image split in interleaved 8-row stripes over %d GPU(s), scene replicated, %s" % (
+             n_gpus, "pixels stored into rank 0's frame over NVLink peer memory by the render kernel + arrival flags (no collective)"
+             if peer else ("NCCL gather to rank 0" if n_gpus > 1 else "single launch")),
          "l2": "flushed between frames (256 MiB memset); per-frame CUDA events"}
     c.update(extra)
     return c
@@ -151,7 +153,7 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     from python_raytracer_b200 import GpuCamera, Settings
-    from python_raytracer_b200.parallel import FrameRenderer
+    from python_raytracer_b200.parallel import FrameRenderer, PeerFrameRenderer
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the GPU path has no CPU fallback")
@@ -163,7 +165,22 @@ def run_ours(args, rank, world, local_rank):
     s = Settings.from_object(C3_SETTINGS)
     cam = GpuCamera(s, device=local_rank, background_function=BUILTIN_BG, background=BUILTIN_BG)
     cam.set_world_dense(origin, cells, poses[0]["chunk_res"], mats)
-    fr = FrameRenderer(cam, rank, world)
+    # N > 1: the render kernel stores finished pixels straight into rank 0's frame over NVLink peer memory and raises
+    # an arrival flag (PeerFrameRenderer); N == 1: the band is the frame.  --gather nccl keeps the NCCL gather (A/B).
+    use_peer = world > 1 and args.gather == "peer"
+    fr = PeerFrameRenderer(cam, rank, world) if use_peer else FrameRenderer(cam, rank, world)
+
+    def render_and_assemble(e1=None):
+        if use_peer:
+            b = fr.render_frame(prepare=False)
+            if e1 is not None:
+                e1.record()
+            fr.release(b)
+        else:
+            fr.render(prepare=False)
+            if e1 is not None:
+                e1.record()
+            fr.gather()
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     rays_frame = C3_SETTINGS["width"] * C3_SETTINGS["height"] * C3_SETTINGS["samples"]
 
@@ -184,7 +201,7 @@ def run_ours(args, rank, world, local_rank):
           for _ in range(args.steps)]
     for i in range(args.warmup):
         set_pose(i)
-        fr.render(prepare=False); fr.gather()
+        render_and_assemble()
     barrier()
     sampler = ClockSampler(local_rank) if rank == 0 else None
     l0 = cam.launch_count
@@ -193,9 +210,7 @@ def run_ours(args, rank, world, local_rank):
         flush.zero_()
         e0, e1, e2 = ev[i]
         e0.record()
-        fr.render(prepare=False)
-        e1.record()
-        fr.gather()
+        render_and_assemble(e1)
         e2.record()
     barrier()
     launches = cam.launch_count - l0
@@ -228,6 +243,8 @@ def run_ours(args, rank, world, local_rank):
     h2d = int(mats.shape[0] * 64 + poses[0]["chunk_res"].size + 8 * 8)
     d2h = int(host.numel()) if host is not None else 0
 
+    if use_peer:
+        fr.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -263,7 +280,7 @@ def run_ours(args, rank, world, local_rank):
                             enumerate(["rays", "in_chunk_samples", "void_samples", "hits", "neighbour_probes", "chunk_reevals", "iterations"])}}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "frames_per_sec": 1000.0 / ms_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world),
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world, use_peer),
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": 1000.0 * float(te[0]) / args.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
@@ -290,6 +307,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how bands reach rank 0")
     args = ap.parse_args()
     args.warmup = max(3, args.warmup) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))

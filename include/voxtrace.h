@@ -138,6 +138,28 @@ typedef struct {
  * frame_seed perturbs the Philox streams when settings.static is 0; ignored when it is 1. */
 int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
               uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed);
+/* ---- multi-GPU frame assembly over peer memory (replaces the pool's result pipes, init.py:185-190, 205) -------
+ * One process per GPU.  Rank 0 owns the full frame(s) and an array of arrival flags in memory from vt_shared_alloc;
+ * the other ranks open them with CUDA IPC and render with a FRAME TARGET: every finished pixel is stored at
+ * frame[(y * width + x) * 4] -- a store over NVLink when the frame is a peer's -- and when a rank's launch is
+ * complete its last warp publishes `arrive_value` in its arrival flag (system-scope fence first).  Rank 0 queues
+ * vt_stream_wait_flags on its stream instead of a collective.  Flag values only grow (frame numbers).
+ * vt_stream_signal_flags is the reverse direction (rank 0 hands a frame buffer back to the renderers). */
+int vt_shared_alloc(vt_ctx *ctx, int64_t bytes, void **out_dev_ptr);     /* zero-filled, plain cudaMalloc */
+int vt_shared_free(vt_ctx *ctx, void *dev_ptr);
+int vt_ipc_export(vt_ctx *ctx, void *dev_ptr, uint8_t handle[64]);
+int vt_ipc_open(vt_ctx *ctx, const uint8_t handle[64], void **out_dev_ptr);
+int vt_ipc_close(vt_ctx *ctx, void *dev_ptr);
+/* dev_frame NULL switches the target off.  Rectangle regions only; dev_rgba8 of vt_render may then be NULL. */
+int vt_set_frame_target(vt_ctx *ctx, uint8_t *dev_frame, uint32_t *dev_arrive_flag, uint32_t arrive_value);
+/* Stream-ordered: continue once flags[0..n) have all reached `value` (n <= 32).  A wait longer than timeout_s
+ * (default 2 s) gives up and records 1 + flag index for vt_wait_status instead of hanging the GPU. */
+int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t value, double timeout_s);
+/* Stream-ordered: store `value` into n flags (n <= 16) given by a HOST array of device pointers (peers' memory). */
+int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_flag_ptrs, int n, uint32_t value);
+int vt_wait_status(vt_ctx *ctx, int *status);                            /* synchronises; 0 = no wait timed out */
+int vt_copy_to_host(vt_ctx *ctx, void *host_dst, const void *dev_src, int64_t bytes);   /* async on the ctx stream */
+
 /* Number of output pixels a region produces (host arithmetic only). */
 int64_t vt_region_pixels(const vt_region *region);
 /* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */

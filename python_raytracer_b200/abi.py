@@ -14,7 +14,9 @@ RAY_RECORD = 16
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
            "vt_set_settings", "vt_set_materials", "vt_set_camera", "vt_set_world", "vt_set_chunk_table",
            "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
-           "vt_launch_count", "vt_build_world", "vt_goxel_parse", "vt_free")
+           "vt_launch_count", "vt_build_world", "vt_goxel_parse", "vt_free",
+           "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
+           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_wait_status", "vt_copy_to_host")
 
 
 class VtSettings(C.Structure):
@@ -79,6 +81,16 @@ def load(path: str | None = None):
         "vt_goxel_parse": (C.c_int, [C.c_char_p, C.c_int32, C.POINTER(C.c_char_p), i32, C.POINTER(C.POINTER(C.c_int32)),
                                      C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(i64), C.c_char_p, i32]),
         "vt_free": (None, [vp]),
+        "vt_shared_alloc": (C.c_int, [vp, i64, C.POINTER(vp)]),
+        "vt_shared_free": (C.c_int, [vp, vp]),
+        "vt_ipc_export": (C.c_int, [vp, vp, C.c_char_p]),
+        "vt_ipc_open": (C.c_int, [vp, C.c_char_p, C.POINTER(vp)]),
+        "vt_ipc_close": (C.c_int, [vp, vp]),
+        "vt_set_frame_target": (C.c_int, [vp, vp, vp, C.c_uint32]),
+        "vt_stream_wait_flags": (C.c_int, [vp, vp, i32, C.c_uint32, C.c_double]),
+        "vt_stream_signal_flags": (C.c_int, [vp, C.POINTER(vp), i32, C.c_uint32]),
+        "vt_wait_status": (C.c_int, [vp, C.POINTER(C.c_int)]),
+        "vt_copy_to_host": (C.c_int, [vp, vp, vp, i64]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

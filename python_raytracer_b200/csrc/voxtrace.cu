@@ -185,6 +185,27 @@ __global__ void build_world_kernel(const vt_object *__restrict__ objs, int n, in
     }
 }
 
+// Peer-memory handshakes of the multi-GPU frame path.  Flags are u32 words in cudaMalloc'ed memory
+// that peers reach through CUDA IPC; values only grow (frame sequence numbers), so a waiter never misses one.
+__global__ void wait_flags_kernel(const unsigned int *flags, int n, unsigned int value, long long timeout_cycles, int *status) {
+    const int t = threadIdx.x;
+    if (t >= n) return;
+    const long long t0 = clock64();
+    while ((int)(*(volatile const unsigned int *)(flags + t) - value) < 0) {
+        if (clock64() - t0 > timeout_cycles) { atomicExch(status, 1 + t); return; }
+        __nanosleep(200);
+    }
+    __threadfence_system();
+}
+
+struct FlagTargets { unsigned int *p[16]; };
+__global__ void signal_flags_kernel(FlagTargets tg, int n, unsigned int value) {
+    const int t = threadIdx.x;
+    if (t >= n || !tg.p[t]) return;
+    __threadfence_system();
+    atomicExch_system(tg.p[t], value);
+}
+
 // ------------------------------------------------------------------------------------------------------
 // host side: context + C ABI
 
@@ -225,6 +246,9 @@ struct vt_ctx {
     int kernel_version = 2;                                         // VT_KERNEL=1 selects the v1 warp-tile kernel (A/B)
     int brick_runs = 1;                                             // VT_RUNS=0 disables empty-brick runs (A/B)
     int refill_min = 32;                                            // VT_REFILL overrides
+    // multi-GPU frame target (vt_set_frame_target) and the status word of the wait kernel
+    uint8_t *frame_target = nullptr; unsigned int *arrive_flag = nullptr; unsigned int arrive_value = 0;
+    int *d_wait_status = nullptr; int clock_khz = 0;
     // region row map
     int32_t *d_row_y = nullptr; int row_cap = 0;
     std::vector<int32_t> h_row_y; int row_key[7] = {-1, -1, -1, -1, -1, -1, -1};
@@ -292,7 +316,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_world(ctx);
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
-    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
+    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_wait_status); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -515,6 +539,95 @@ extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t
     return 0;
 }
 
+// ---- multi-GPU: peer-visible frame + flags ---------------------------------------------------------------
+extern "C" int vt_shared_alloc(vt_ctx *ctx, int64_t bytes, void **out) {
+    if (!ctx || !out || bytes <= 0) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaMalloc(out, (size_t)bytes));            // plain cudaMalloc: base pointer == IPC handle base
+    VT_CHECK(ctx, cudaMemset(*out, 0, (size_t)bytes));
+    return 0;
+}
+extern "C" int vt_shared_free(vt_ctx *ctx, void *p) {
+    if (!ctx) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    VT_CHECK(ctx, cudaFree(p));
+    return 0;
+}
+extern "C" int vt_ipc_export(vt_ctx *ctx, void *dev_ptr, uint8_t handle[64]) {
+    if (!ctx || !dev_ptr || !handle) return 1;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    VT_CHECK(ctx, cudaIpcGetMemHandle(&h, dev_ptr));
+    memcpy(handle, &h, 64);
+    return 0;
+}
+extern "C" int vt_ipc_open(vt_ctx *ctx, const uint8_t handle[64], void **out) {
+    if (!ctx || !handle || !out) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    VT_CHECK(ctx, cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return 0;
+}
+extern "C" int vt_ipc_close(vt_ctx *ctx, void *p) {
+    if (!ctx) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    VT_CHECK(ctx, cudaIpcCloseMemHandle(p));
+    return 0;
+}
+extern "C" int vt_set_frame_target(vt_ctx *ctx, uint8_t *dev_frame, uint32_t *dev_arrive_flag, uint32_t arrive_value) {
+    if (!ctx) return 1;
+    ctx->frame_target = dev_frame; ctx->arrive_flag = dev_frame ? dev_arrive_flag : nullptr; ctx->arrive_value = arrive_value;
+    return 0;
+}
+extern "C" int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t value, double timeout_s) {
+    if (!ctx || !dev_flags || n < 1 || n > 32) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->d_wait_status) {
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_wait_status, sizeof(int)));
+        VT_CHECK(ctx, cudaMemsetAsync(ctx->d_wait_status, 0, sizeof(int), ctx->stream));
+    }
+    if (ctx->clock_khz == 0) {                 // queried once: this attribute is slow to read (~1 ms)
+        int khz = 0;
+        cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, ctx->device);
+        ctx->clock_khz = khz > 0 ? khz : 1500000;
+    }
+    long long cycles = (long long)((timeout_s > 0 ? timeout_s : 2.0) * 1e3 * (double)ctx->clock_khz);
+    wait_flags_kernel<<<1, 32, 0, ctx->stream>>>(dev_flags, n, value, cycles, ctx->d_wait_status);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+extern "C" int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_ptrs, int n, uint32_t value) {
+    if (!ctx || !host_ptrs || n < 1 || n > 16) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    FlagTargets tg;
+    memset(&tg, 0, sizeof tg);
+    for (int k = 0; k < n; k++) tg.p[k] = host_ptrs[k];
+    signal_flags_kernel<<<1, 32, 0, ctx->stream>>>(tg, n, value);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+extern "C" int vt_wait_status(vt_ctx *ctx, int *status) {
+    if (!ctx || !status) return 1;
+    *status = 0;
+    if (!ctx->d_wait_status) return 0;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaMemcpyAsync(status, ctx->d_wait_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    return 0;
+}
+extern "C" int vt_copy_to_host(vt_ctx *ctx, void *host_dst, const void *dev_src, int64_t bytes) {
+    if (!ctx || !host_dst || !dev_src || bytes < 0) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaMemcpyAsync(host_dst, dev_src, (size_t)bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    return 0;
+}
+
 extern "C" int vt_world_stats(vt_ctx *ctx, int64_t *n_bricks, int64_t *bytes) {
     if (!ctx) return 1;
     long long live = ctx->pool_used - (long long)ctx->free_slots.size();
@@ -714,6 +827,9 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
         P.n_pixels = (long long)band_rows * (region->x1 - region->x0);
     }
     if (P.n_pixels == 0) return 0;
+    P.frame_target = ctx->frame_target; P.arrive_flag = ctx->arrive_flag; P.arrive_value = ctx->arrive_value;
+    if (ctx->frame_target && (ctx->kernel_version == 1 || region->dev_pixels))
+        return fail(ctx, "vt_render: a frame target needs the persistent kernel and a rectangle region");
     P.rgba8 = dev_rgba8; P.mean = dev_mean; P.ray0 = dev_ray0; P.visited = dev_visited;
     P.counters = reinterpret_cast<unsigned long long *>(dev_counters);
     // lanes per pixel: samples rounded up to a power of two (<= 32); pixels per warp form a small 2-D tile

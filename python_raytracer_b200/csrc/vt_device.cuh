@@ -63,6 +63,10 @@ struct DevParams {
     int brick_runs;                 // 1: chunk_size % 8 == 0, empty-brick runs allowed (VT_RUNS=0 disables, A/B)
     uint32_t lod_magic[VT_LOD_TAB + 1];   // floor(n / r) == umulhi(n, magic[r]) for n < 2^24 / r ... (r >= 2)
     int32_t lod_bias[VT_LOD_TAB + 1][3];  // world origin mod r per axis
+    // multi-GPU frame target: full [height][width] RGBA8 frame (possibly in a peer GPU's memory) + arrival flag
+    uint8_t *frame_target;
+    unsigned int *arrive_flag;
+    unsigned int arrive_value;
     // outputs
     uint8_t *rgba8;
     float *mean;

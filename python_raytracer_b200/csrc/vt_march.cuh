@@ -379,11 +379,14 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
         double dn = i2d(n);
         double mr = u2d((uint32_t)sr) / dn, mg = u2d((uint32_t)sg) / dn, mb = u2d((uint32_t)sb) / dn, ma = u2d((uint32_t)sa) / dn;
         if (P.mean) reinterpret_cast<float4 *>(P.mean)[i] = make_float4((float)mr, (float)mg, (float)mb, (float)ma);
-        if (P.rgba8) {
+        if (P.rgba8 || P.frame_target) {
             uchar4 q;                                                        // truncation, like a C cast
             q.x = (unsigned char)floor_i(fmin(255.0, mr)); q.y = (unsigned char)floor_i(fmin(255.0, mg));
             q.z = (unsigned char)floor_i(fmin(255.0, mb)); q.w = (unsigned char)floor_i(fmin(255.0, ma));
-            reinterpret_cast<uchar4 *>(P.rgba8)[i] = q;
+            // frame target (multi-GPU): the pixel goes straight to its place in the full frame, which may live on a
+            // peer GPU (NVLink store), instead of this rank's compact band
+            const size_t o = P.frame_target ? (size_t)y * (size_t)s.width + (size_t)x : i;
+            reinterpret_cast<uchar4 *>(P.frame_target ? P.frame_target : P.rgba8)[o] = q;
         }
     }
 }
@@ -525,11 +528,16 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
             if (lane == 0 && t) atomicAdd(P.counters + k, (unsigned long long)t);
         }
     }
-    // the last warp to leave resets the queue for the next launch
+    // The last warp to leave resets the queue for the next launch and, with a frame target, publishes the arrival
+    // flag: every thread's pixel stores are fenced at system scope first, so the peer that sees the flag sees the band.
+    if (P.arrive_flag) { __threadfence_system(); __syncwarp(full); }
     if (lane == 0) {
         __threadfence();
         unsigned long long done = atomicAdd(P.queue + 1, 1ull);
-        if (done == (unsigned long long)P.total_warps - 1ull) { P.queue[0] = 0ull; P.queue[1] = 0ull; }
+        if (done == (unsigned long long)P.total_warps - 1ull) {
+            P.queue[0] = 0ull; P.queue[1] = 0ull;
+            if (P.arrive_flag) { __threadfence_system(); atomicExch_system(P.arrive_flag, P.arrive_value); }
+        }
     }
 }
 

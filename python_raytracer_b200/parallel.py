@@ -88,3 +88,145 @@ class FrameRenderer(StripeGather):
             host_rgba8.copy_(frame, non_blocking=True)
         torch.cuda.current_stream(self.cam.device).synchronize()
         return host_rgba8
+
+
+# ------------------------------------------------------------------------------------------------------------
+# Frame assembly over NVLink peer memory: the render kernel itself delivers the pixels (no collective per frame).
+
+class _DevView:
+    """Raw device pointer -> torch tensor view (no copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr, shape, typestr="|u1"):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+class PeerFrameRenderer:
+    """One rank of the multi-GPU frame path with the gather fused into the render kernel.
+
+    Rank 0 owns ``buffers`` full frames and the arrival flags (cudaMalloc'ed by libvoxtrace, exported with CUDA IPC);
+    every other rank opens them and renders its stripes with a *frame target*: finished pixels are stored straight
+    into rank 0's frame over NVLink and the last warp of the launch raises the rank's arrival flag.  Rank 0 queues
+    a flag wait on its stream where the NCCL gather used to be.  A frame buffer is handed back to the renderers
+    with a credit flag in each renderer's own memory, so nobody overwrites a frame rank 0 is still reading.
+    The reference's equivalent is the pool's result pipe + ``draw_tile`` (init.py:185-190, 205).
+    """
+
+    FLAGS_PER_BUFFER = 32
+
+    def __init__(self, cam, rank: int, world: int, stripe: int = STRIPE_ROWS, buffers: int = 2):
+        import ctypes as C
+        self.cam, self.rank, self.world, self.stripe, self.buffers = cam, rank, world, stripe, buffers
+        self.w, self.h = int(cam.settings.width), int(cam.settings.height)
+        self.frame_no = 0
+        self._C = C
+        lib, ctx = cam._lib, cam._ctx
+        nbytes = self.w * self.h * 4
+        mine = []                      # (kind, ptr) owned by this rank
+        handles = {}
+        if rank == 0:
+            self.frames = []
+            for b in range(buffers):
+                p = C.c_void_p()
+                cam._check(lib.vt_shared_alloc(ctx, nbytes, C.byref(p)))
+                self.frames.append(p.value)
+            p = C.c_void_p()
+            cam._check(lib.vt_shared_alloc(ctx, 4 * self.FLAGS_PER_BUFFER * buffers, C.byref(p)))
+            self.arrive = p.value
+            for k, ptr in enumerate(self.frames + [self.arrive]):
+                hb = C.create_string_buffer(64)
+                cam._check(lib.vt_ipc_export(ctx, C.c_void_p(ptr), hb))
+                handles[k] = hb.raw
+            self.frame_views = [torch.as_tensor(_DevView(f, (self.h, self.w, 4)), device=cam.device) for f in self.frames]
+        else:
+            p = C.c_void_p()
+            cam._check(lib.vt_shared_alloc(ctx, 4 * buffers, C.byref(p)))
+            self.credit = p.value
+            hb = C.create_string_buffer(64)
+            cam._check(lib.vt_ipc_export(ctx, C.c_void_p(self.credit), hb))
+            handles["credit"] = hb.raw
+        gathered = [None] * world
+        if world > 1:
+            dist.all_gather_object(gathered, handles)
+        else:
+            gathered = [handles]
+        self._opened = []
+        if rank == 0:
+            self.peer_credit = [None]
+            for r in range(1, world):
+                q = C.c_void_p()
+                cam._check(lib.vt_ipc_open(ctx, gathered[r]["credit"], C.byref(q)))
+                self.peer_credit.append(q.value)
+                self._opened.append(q.value)
+        else:
+            self.frames = []
+            for k in range(buffers + 1):
+                q = C.c_void_p()
+                cam._check(lib.vt_ipc_open(ctx, gathered[0][k], C.byref(q)))
+                self._opened.append(q.value)
+                (self.frames.append(q.value) if k < buffers else setattr(self, "arrive", q.value))
+
+    def _flag(self, b, r):
+        return self.arrive + 4 * (b * self.FLAGS_PER_BUFFER + r)
+
+    def render_frame(self, prepare=True):
+        """Renders this rank's stripes of the next frame into rank 0's frame buffer.  Returns the buffer index."""
+        C = self._C
+        cam, lib, ctx = self.cam, self.cam._lib, self.cam._ctx
+        f = self.frame_no
+        b, k = f % self.buffers, f // self.buffers
+        if prepare:
+            cam._prepare()
+        if self.rank > 0 and k > 0:            # buffer b must have been released k times by rank 0
+            cam._check(lib.vt_stream_wait_flags(ctx, C.c_void_p(self.credit + 4 * b), 1, k, 30.0))
+        cam._check(lib.vt_set_frame_target(ctx, C.c_void_p(self.frames[b]), C.c_void_p(self._flag(b, self.rank)), f + 1))
+        try:
+            cam.render(stripes=(self.stripe, self.world, self.rank), want=(), prepare=False)
+        finally:
+            cam._check(lib.vt_set_frame_target(ctx, None, None, 0))
+        if self.rank == 0 and self.world > 1:
+            cam._check(lib.vt_stream_wait_flags(ctx, C.c_void_p(self._flag(b, 1)), self.world - 1, f + 1, 30.0))
+        self.frame_no += 1
+        return b
+
+    def release(self, b):
+        """Rank 0: frame buffer b has been consumed (stream-ordered); the renderers may overwrite it."""
+        if self.rank != 0 or self.world == 1:
+            return
+        C = self._C
+        k = (self.frame_no - 1) // self.buffers + 1
+        arr = (C.c_void_p * (self.world - 1))(*[p + 4 * b for p in self.peer_credit[1:]])
+        self.cam._check(self.cam._lib.vt_stream_signal_flags(self.cam._ctx, arr, self.world - 1, k))
+
+    def frame_to_host(self, pos, rot, chunk_res, host_rgba8):
+        """Same contract as FrameRenderer.frame_to_host, without the per-frame collective."""
+        self.cam.pos, self.cam.rot = pos, rot
+        if chunk_res is not None:
+            self.cam.set_chunk_res(chunk_res)
+        b = self.render_frame(prepare=True)
+        if self.rank == 0:
+            host_rgba8.copy_(self.frame_views[b], non_blocking=True)
+            self.release(b)
+            torch.cuda.current_stream(self.cam.device).synchronize()
+        return host_rgba8
+
+    def wait_status(self) -> int:
+        C = self._C
+        st = C.c_int(0)
+        self.cam._check(self.cam._lib.vt_wait_status(self.cam._ctx, C.byref(st)))
+        return st.value
+
+    def close(self):
+        lib, ctx, C = self.cam._lib, self.cam._ctx, self._C
+        torch.cuda.synchronize(self.cam.device)
+        if self.world > 1:
+            dist.barrier()
+        for p in self._opened:
+            lib.vt_ipc_close(ctx, C.c_void_p(p))
+        if self.world > 1:
+            dist.barrier()
+        if self.rank == 0:
+            self.frame_views = None
+            for p in self.frames + [self.arrive]:
+                lib.vt_shared_free(ctx, C.c_void_p(p))
+        else:
+            lib.vt_shared_free(ctx, C.c_void_p(self.credit))

@@ -1,0 +1,55 @@
+"""Multi-GPU check of the peer-memory frame path (run under torchrun on a box with >= 2 GPUs; not collected by pytest):
+   torchrun --nproc-per-node N tests/mgpu_peer_check.py
+Every rank renders its stripes straight into rank 0's frame; rank 0 compares 6 frames (two buffers, three rounds, the
+camera moving) with its own single-GPU render of the same frames and with the NCCL-gather path, bit for bit."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench
+from python_raytracer_b200 import GpuCamera, Settings
+from python_raytracer_b200.parallel import FrameRenderer, PeerFrameRenderer
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    origin, cells, mats, poses = bench.load_workload()
+    sd = dict(bench.C3_SETTINGS); sd.update(width=960, height=540)
+    cam = GpuCamera(Settings.from_object(sd), device=local, background_function=bench.BUILTIN_BG, background=bench.BUILTIN_BG)
+    cam.set_world_dense(origin, cells, poses[0]["chunk_res"], mats)
+    peer = PeerFrameRenderer(cam, rank, world)
+    nccl = FrameRenderer(cam, rank, world)
+    host = torch.empty((540, 960, 4), dtype=torch.uint8).pin_memory()
+    host2 = torch.empty((540, 960, 4), dtype=torch.uint8).pin_memory()
+    bad = 0
+    for f in range(6):
+        p = poses[f % len(poses)]
+        peer.frame_to_host(p["pos"], p["rot"], p["chunk_res"], host)
+        nccl.frame_to_host(p["pos"], p["rot"], p["chunk_res"], host2)
+        if rank == 0:
+            cam.pos, cam.rot = p["pos"], p["rot"]
+            single = cam.render(want=("rgba8",))["rgba8"].cpu()
+            ok1, ok2 = torch.equal(single, host), torch.equal(single, host2)
+            print("frame %d  peer==single %s  nccl==single %s" % (f, ok1, ok2), flush=True)
+            bad += (not ok1) + (not ok2)
+    st = peer.wait_status()
+    t = torch.tensor([bad + (st != 0)], device=dev)
+    dist.all_reduce(t)
+    peer.close()
+    cam.close()
+    dist.destroy_process_group()
+    if rank == 0:
+        print("PEER CHECK", "OK" if int(t) == 0 else "FAILED", flush=True)
+    sys.exit(0 if int(t) == 0 else 1)
+
+
+if __name__ == "__main__":
+    main()
