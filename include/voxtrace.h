@@ -160,6 +160,26 @@ int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_flag_ptrs, int n, 
 int vt_wait_status(vt_ctx *ctx, int *status);                            /* synchronises; 0 = no wait timed out */
 int vt_copy_to_host(vt_ctx *ctx, void *host_dst, const void *dev_src, int64_t bytes);   /* async on the ctx stream */
 
+/* ---- image-space steps after the path: Window.draw_tile / Window.draw (init.py:185-190, 207-253) ----------------
+ * pygame's own rounding is unpinned; the formulas are stated in csrc/vt_postfx.cuh. */
+typedef struct {
+    int32_t width, height;         /* canvas = settings.window */
+    int32_t out_width, out_height; /* settings.window_scaled (data.py:65) */
+    int32_t iris_on;               /* settings.iris and settings.iris_time (init.py:219) */
+    int32_t reserved;
+    double spill;                  /* settings.spill, 0 = off (init.py:213) */
+    double iris;                   /* Window.iris, the adaptation state (init.py:220-222, 462) */
+    double bloom, bloom_blur;      /* settings.bloom, settings.bloom_blur, 0 = off (init.py:232) */
+    double subsamples;             /* settings.subsamples (init.py:242-244) */
+    double smooth;                 /* settings.smooth: 0 nearest, 1 smooth, else sharp-then-smooth (init.py:247-254) */
+} vt_fx;
+/* draw_tile: alpha-blit one tile (RGBA8, alpha 0 where the tile has no pixel) onto the canvas, n_pixels each. */
+int vt_fx_compose(vt_ctx *ctx, uint8_t *dev_canvas, const uint8_t *dev_tile, int64_t n_pixels);
+/* draw: spill, iris, bloom, subsampling and scaling of a COPY of the canvas into dev_out [out_height][out_width][4].
+ * host_avg receives transform.average_color(canvas, consider_alpha=True), which the caller needs for
+ * iris_target = 1 - max(r, g, b) / 255 * 2 (init.py:229).  Synchronises the stream. */
+int vt_fx_draw(vt_ctx *ctx, const vt_fx *fx, const uint8_t *dev_canvas, uint8_t *dev_out, int32_t host_avg[4]);
+
 /* Number of output pixels a region produces (host arithmetic only). */
 int64_t vt_region_pixels(const vt_region *region);
 /* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */

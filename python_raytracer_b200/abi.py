@@ -16,7 +16,7 @@ EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set
            "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
            "vt_launch_count", "vt_build_world", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
-           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_wait_status", "vt_copy_to_host")
+           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
 
 
 class VtSettings(C.Structure):
@@ -37,6 +37,12 @@ class VtRegion(C.Structure):
 class VtObject(C.Structure):
     _fields_ = [("dev_sprite", C.c_void_p), ("size", C.c_int32 * 3), ("mins", C.c_int32 * 3), ("maxs", C.c_int32 * 3),
                 ("angle", C.c_int32 * 3), ("reserved", C.c_int32)]
+
+
+class VtFx(C.Structure):
+    _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("out_width", C.c_int32), ("out_height", C.c_int32),
+                ("iris_on", C.c_int32), ("reserved", C.c_int32), ("spill", C.c_double), ("iris", C.c_double),
+                ("bloom", C.c_double), ("bloom_blur", C.c_double), ("subsamples", C.c_double), ("smooth", C.c_double)]
 
 
 class VoxtraceError(RuntimeError):
@@ -91,6 +97,8 @@ def load(path: str | None = None):
         "vt_stream_signal_flags": (C.c_int, [vp, C.POINTER(vp), i32, C.c_uint32]),
         "vt_wait_status": (C.c_int, [vp, C.POINTER(C.c_int)]),
         "vt_copy_to_host": (C.c_int, [vp, vp, vp, i64]),
+        "vt_fx_compose": (C.c_int, [vp, vp, vp, i64]),
+        "vt_fx_draw": (C.c_int, [vp, C.POINTER(VtFx), vp, vp, C.POINTER(C.c_int32)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)

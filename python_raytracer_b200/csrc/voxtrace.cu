@@ -249,6 +249,9 @@ struct vt_ctx {
     // multi-GPU frame target (vt_set_frame_target) and the status word of the wait kernel
     uint8_t *frame_target = nullptr; unsigned int *arrive_flag = nullptr; unsigned int arrive_value = 0;
     int *d_wait_status = nullptr; int clock_khz = 0;
+    // post-FX scratch (vt_fx_draw): grow-only device buffers
+    uint8_t *fx_buf[4] = {nullptr, nullptr, nullptr, nullptr}; long long fx_cap[4] = {0, 0, 0, 0};
+    unsigned long long *d_fx_sums = nullptr; int *d_fx_avg = nullptr;
     // region row map
     int32_t *d_row_y = nullptr; int row_cap = 0;
     std::vector<int32_t> h_row_y; int row_key[7] = {-1, -1, -1, -1, -1, -1, -1};
@@ -316,7 +319,9 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_world(ctx);
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
-    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_wait_status); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
+    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_wait_status);
+    for (int k = 0; k < 4; k++) cudaFree(ctx->fx_buf[k]);
+    cudaFree(ctx->d_fx_sums); cudaFree(ctx->d_fx_avg); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -857,5 +862,111 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
     }
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+
+// ---- post-FX (vt_postfx.cuh) ------------------------------------------------------------------------------
+#include "vt_postfx.cuh"
+
+static int fx_grid(long long n) { long long g = (n + 255) / 256; return (int)(g < 148LL * 16 ? (g > 0 ? g : 1) : 148LL * 16); }
+
+static int fx_buffer(vt_ctx *ctx, int k, long long bytes, uchar4 **out) {
+    if (bytes > ctx->fx_cap[k]) {
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->fx_buf[k]); ctx->fx_buf[k] = nullptr; ctx->fx_cap[k] = 0;
+        VT_CHECK(ctx, cudaMalloc(&ctx->fx_buf[k], (size_t)bytes));
+        ctx->fx_cap[k] = bytes;
+    }
+    *out = reinterpret_cast<uchar4 *>(ctx->fx_buf[k]);
+    return 0;
+}
+
+extern "C" int vt_fx_compose(vt_ctx *ctx, uint8_t *dev_canvas, const uint8_t *dev_tile, int64_t n) {
+    if (!ctx || !dev_canvas || !dev_tile || n < 0) return 1;
+    if (n == 0) return 0;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    vtfx::compose_kernel<<<fx_grid(n), 256, 0, ctx->stream>>>(reinterpret_cast<uchar4 *>(dev_canvas), reinterpret_cast<const uchar4 *>(dev_tile), n);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+
+// one pygame scaling call: nearest (transform.scale), or "smooth" = area average when shrinking on both axes, bilinear otherwise
+static int fx_scale(vt_ctx *ctx, const uchar4 *src, int sw, int sh, uchar4 *dst, int dw, int dh, bool smooth) {
+    const long long n = (long long)dw * dh;
+    if (smooth && dw < sw && dh < sh) vtfx::shrink_kernel<<<fx_grid(n), 256, 0, ctx->stream>>>(src, sw, sh, dst, dw, dh);
+    else vtfx::resample_kernel<<<fx_grid(n), 256, 0, ctx->stream>>>(src, sw, sh, dst, dw, dh, smooth ? 1 : 0, nullptr);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+
+extern "C" int vt_fx_draw(vt_ctx *ctx, const vt_fx *fx, const uint8_t *dev_canvas, uint8_t *dev_out, int32_t host_avg[4]) {
+    if (!ctx || !fx || !dev_canvas || !dev_out) return 1;
+    const int W = fx->width, H = fx->height, OW = fx->out_width, OH = fx->out_height;
+    if (W <= 0 || H <= 0 || OW <= 0 || OH <= 0 || W > 65535 || H > 65535 || OW > 65535 || OH > 65535)
+        return fail(ctx, "vt_fx_draw: canvas / window size out of range");
+    if (fx->smooth < 0 || fx->subsamples < 0 || fx->subsamples > 15) return fail(ctx, "vt_fx_draw: smooth / subsamples out of range");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const long long n = (long long)W * H;
+    if (!ctx->d_fx_sums) {
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_fx_sums, 4 * sizeof(unsigned long long)));
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_fx_avg, 4 * sizeof(int)));
+    }
+    const uchar4 *canvas = reinterpret_cast<const uchar4 *>(dev_canvas);
+    VT_CHECK(ctx, cudaMemsetAsync(ctx->d_fx_sums, 0, 4 * sizeof(unsigned long long), ctx->stream));
+    vtfx::average_kernel<<<fx_grid(n), 256, 0, ctx->stream>>>(canvas, n, ctx->d_fx_sums);
+    ctx->launches++;
+    vtfx::FxParams p;
+    p.spill_fac = fx->spill != 0.0 ? 255 - (int)nearbyint(fx->spill * 255.0) : -1;
+    p.iris_on = fx->iris_on ? 1 : 0;
+    p.iris_add = fx->iris > 0.0 ? 1 : 0;
+    p.iris_fac = (int)nearbyint(fabs(fx->iris * 255.0));
+    const bool bloom = fx->bloom != 0.0 && fx->bloom_blur != 0.0;
+    p.bloom_fac = bloom ? (int)nearbyint((1.0 - fx->bloom) * 255.0) : -1;
+    uchar4 *a = nullptr, *dark = nullptr, *small = nullptr, *big = nullptr;
+    if (int rc = fx_buffer(ctx, 0, n * 4, &a)) return rc;
+    if (bloom) if (int rc = fx_buffer(ctx, 1, n * 4, &dark)) return rc;
+    vtfx::spill_iris_kernel<<<fx_grid(n), 256, 0, ctx->stream>>>(canvas, n, ctx->d_fx_sums, p, a, dark, ctx->d_fx_avg);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    if (bloom) {                                                                  // init.py:232-239
+        double div = fx->bloom_blur > 1.0 ? fx->bloom_blur : 1.0;
+        int bw = (int)nearbyint((double)W / div), bh = (int)nearbyint((double)H / div);
+        if (bw < 1) bw = 1;
+        if (bh < 1) bh = 1;
+        if (int rc = fx_buffer(ctx, 2, (long long)bw * bh * 4, &small)) return rc;
+        if (int rc = fx_scale(ctx, dark, W, H, small, bw, bh, true)) return rc;
+        vtfx::resample_kernel<<<fx_grid(n), 256, 0, ctx->stream>>>(small, bw, bh, a, W, H, 1, a);      // smoothscale up, blit ADD
+        ctx->launches++;
+        VT_CHECK(ctx, cudaGetLastError());
+    }
+    const uchar4 *cur = a;
+    int cw = W, ch = H;
+    uchar4 *out = reinterpret_cast<uchar4 *>(dev_out);
+    if (fx->subsamples != 0.0) {                                                  // init.py:242-244
+        const double f = 1.0 + fx->subsamples;
+        int nw = (int)((double)W * f), nh = (int)((double)H * f);
+        if (int rc = fx_buffer(ctx, 1, (long long)nw * nh * 4, &dark)) return rc;
+        if (int rc = fx_scale(ctx, cur, cw, ch, dark, nw, nh, true)) return rc;
+        cur = dark; cw = nw; ch = nh;
+    }
+    if (fx->smooth == 0.0) {                                                      // init.py:247-254
+        if (int rc = fx_scale(ctx, cur, cw, ch, out, OW, OH, false)) return rc;
+    } else if (fx->smooth == 1.0) {
+        if (int rc = fx_scale(ctx, cur, cw, ch, out, OW, OH, true)) return rc;
+    } else {
+        int f = (int)(1.0 / fx->smooth);
+        if (f < 1) f = 1;
+        const long long nw = (long long)cw * f, nh = (long long)ch * f;
+        if (nw > 65535 || nh > 65535) return fail(ctx, "vt_fx_draw: sharp pre-scale too large");
+        if (int rc = fx_buffer(ctx, 3, nw * nh * 4, &big)) return rc;
+        if (int rc = fx_scale(ctx, cur, cw, ch, big, (int)nw, (int)nh, false)) return rc;
+        if (int rc = fx_scale(ctx, big, (int)nw, (int)nh, out, OW, OH, true)) return rc;
+    }
+    int avg[4] = {0, 0, 0, 0};
+    VT_CHECK(ctx, cudaMemcpyAsync(avg, ctx->d_fx_avg, sizeof avg, cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    if (host_avg) for (int k = 0; k < 4; k++) host_avg[k] = avg[k];
     return 0;
 }
