@@ -515,7 +515,6 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
                 if (leave) looked = march_leave_chunk<FAST, FULL_TAIL, COUNT>(P, L, c, ix, iy, iz);
                 __syncwarp(full);
                 if (lane_state(L) == ST_MARCH) march_cell<FAST, COUNT>(P, L, c, ix, iy, iz, looked);
-                __syncwarp(full);
                 if (__popc(__ballot_sync(full, lane_state(L) == ST_MARCH)) < thr) break;
             }
         }
