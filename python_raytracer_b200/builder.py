@@ -116,3 +116,26 @@ class WorldBuilder:
         res = lod_table(self.origin, self.present, pos, s.chunk_size, s.chunk_lod, s.dist_max, visible=visible)
         self.cam.set_chunk_res(res)
         return res
+
+
+def scene_from_reference(objects, material_id):
+    """Live reference objects -> SceneObjects, for callers that keep the engine's ``data.objects`` (data.py:430-624).
+
+    ``objects``: iterable of reference ``data.Object`` in ``data.objects`` order; ``material_id``: callable mapping a
+    reference ``Material`` to its device id (``GpuCamera._material_id`` -- it also rejects custom material functions).
+    Only visible objects with a sprite are drawn (init.py:404, data.py:569).  The active frame's voxels are taken
+    through the reference's own ``Sprite.get_voxels`` (which expands sprites stored at a coarser resolution), so the
+    grid answers exactly what ``Sprite.get_voxel`` would for positions inside the sprite box."""
+    out = []
+    for obj in objects:
+        spr = obj.get_sprite() if hasattr(obj, "get_sprite") else getattr(obj, "sprite", None)
+        if not spr or not getattr(obj, "visible", True):
+            continue
+        size = (int(spr.size.x), int(spr.size.y), int(spr.size.z))
+        grid = np.zeros(size, np.uint8)
+        for (x, y, z), mat in spr.get_voxels(None).items():
+            if 0 <= x < size[0] and 0 <= y < size[1] and 0 <= z < size[2]:
+                grid[x, y, z] = material_id(mat)
+        out.append(SceneObject(sprite=grid, pos=(float(obj.pos.x), float(obj.pos.y), float(obj.pos.z)),
+                               rot=(float(obj.rot.x), float(obj.rot.y), float(obj.rot.z))))
+    return out
