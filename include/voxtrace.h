@@ -157,6 +157,8 @@ int vt_set_frame_target(vt_ctx *ctx, uint8_t *dev_frame, uint32_t *dev_arrive_fl
 int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t value, double timeout_s);
 /* Stream-ordered: store `value` into n flags (n <= 16) given by a HOST array of device pointers (peers' memory). */
 int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_flag_ptrs, int n, uint32_t value);
+/* Same, on another CUDA stream of the context's device (e.g. the copy stream that reads the frame out). */
+int vt_stream_signal_flags_on(vt_ctx *ctx, void *cuda_stream, uint32_t *const *host_flag_ptrs, int n, uint32_t value);
 int vt_wait_status(vt_ctx *ctx, int *status);                            /* synchronises; 0 = no wait timed out */
 int vt_copy_to_host(vt_ctx *ctx, void *host_dst, const void *dev_src, int64_t bytes);   /* async on the ctx stream */
 

@@ -16,7 +16,7 @@ EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set
            "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
            "vt_launch_count", "vt_build_world", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
-           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
+           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
 
 
 class VtSettings(C.Structure):
@@ -95,6 +95,7 @@ def load(path: str | None = None):
         "vt_set_frame_target": (C.c_int, [vp, vp, vp, C.c_uint32]),
         "vt_stream_wait_flags": (C.c_int, [vp, vp, i32, C.c_uint32, C.c_double]),
         "vt_stream_signal_flags": (C.c_int, [vp, C.POINTER(vp), i32, C.c_uint32]),
+        "vt_stream_signal_flags_on": (C.c_int, [vp, vp, C.POINTER(vp), i32, C.c_uint32]),
         "vt_wait_status": (C.c_int, [vp, C.POINTER(C.c_int)]),
         "vt_copy_to_host": (C.c_int, [vp, vp, vp, i64]),
         "vt_fx_compose": (C.c_int, [vp, vp, vp, i64]),

@@ -209,6 +209,7 @@ __global__ void signal_flags_kernel(FlagTargets tg, int n, unsigned int value) {
 // ------------------------------------------------------------------------------------------------------
 // host side: context + C ABI
 
+#define VT_STAGES 8
 struct vt_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
@@ -249,6 +250,8 @@ struct vt_ctx {
     // multi-GPU frame target (vt_set_frame_target) and the status word of the wait kernel
     uint8_t *frame_target = nullptr; unsigned int *arrive_flag = nullptr; unsigned int arrive_value = 0;
     int *d_wait_status = nullptr; int clock_khz = 0;
+    struct Stage { void *h = nullptr; size_t cap = 0; cudaEvent_t ev = nullptr; };
+    Stage stage[8]; int stage_next = 0;
     // post-FX scratch (vt_fx_draw): grow-only device buffers
     uint8_t *fx_buf[4] = {nullptr, nullptr, nullptr, nullptr}; long long fx_cap[4] = {0, 0, 0, 0};
     unsigned long long *d_fx_sums = nullptr; int *d_fx_avg = nullptr;
@@ -321,6 +324,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
     cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_wait_status);
     for (int k = 0; k < 4; k++) cudaFree(ctx->fx_buf[k]);
+    for (int k = 0; k < VT_STAGES; k++) { if (ctx->stage[k].h) cudaFreeHost(ctx->stage[k].h); if (ctx->stage[k].ev) cudaEventDestroy(ctx->stage[k].ev); }
     cudaFree(ctx->d_fx_sums); cudaFree(ctx->d_fx_avg); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -331,6 +335,7 @@ extern "C" int64_t vt_launch_count(const vt_ctx *ctx) { return ctx ? ctx->launch
 
 extern "C" int vt_set_stream(vt_ctx *ctx, void *cuda_stream) {
     if (!ctx) return 1;
+    if (ctx->stream == (cudaStream_t)cuda_stream) return 0;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     if (ctx->own_stream) { cudaStreamDestroy(ctx->stream); ctx->own_stream = false; }
@@ -360,13 +365,31 @@ extern "C" int vt_set_settings(vt_ctx *ctx, const vt_settings *hs) {
     return 0;
 }
 
+// Small per-frame tables (materials, chunk resolutions) go through a ring of pinned staging slots: the caller's
+// buffer is free on return and the host never waits for the frame in flight.
+static int staged_upload(vt_ctx *ctx, void *dst, const void *src, size_t bytes) {
+    vt_ctx::Stage &st = ctx->stage[ctx->stage_next];
+    ctx->stage_next = (ctx->stage_next + 1) % VT_STAGES;
+    if (st.ev) VT_CHECK(ctx, cudaEventSynchronize(st.ev));
+    else VT_CHECK(ctx, cudaEventCreateWithFlags(&st.ev, cudaEventDisableTiming));
+    if (st.cap < bytes) {
+        if (st.h) cudaFreeHost(st.h);
+        st.h = nullptr; st.cap = 0;
+        size_t cap = bytes < 65536 ? 65536 : bytes;
+        VT_CHECK(ctx, cudaMallocHost(&st.h, cap));
+        st.cap = cap;
+    }
+    memcpy(st.h, src, bytes);
+    VT_CHECK(ctx, cudaMemcpyAsync(dst, st.h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaEventRecord(st.ev, ctx->stream));
+    return 0;
+}
+
 extern "C" int vt_set_materials(vt_ctx *ctx, const vt_material *hm, int n) {
     if (!ctx || !hm) return 1;
     if (n < 0 || n > VT_MAX_MATERIALS) return fail(ctx, "vt_set_materials: at most 255 materials (id 0 is empty)");
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_mats, hm, (size_t)(n + 1) * sizeof(vt_material), cudaMemcpyHostToDevice, ctx->stream));
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));   // host buffer may be reused on return
-    return 0;
+    return staged_upload(ctx, ctx->d_mats, hm, (size_t)(n + 1) * sizeof(vt_material));
 }
 
 extern "C" int vt_set_camera(vt_ctx *ctx, const double pos[3], const double rot[4], double lens) {
@@ -418,9 +441,7 @@ extern "C" int vt_set_chunk_table(vt_ctx *ctx, const uint8_t *host_res, int64_t 
     int mx = 0;
     for (long long k = 0; k < slots; k++) mx = host_res[k] > mx ? host_res[k] : mx;
     ctx->max_res = mx;
-    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_chunk_res, host_res, (size_t)slots, cudaMemcpyHostToDevice, ctx->stream));
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    return 0;
+    return staged_upload(ctx, ctx->d_chunk_res, host_res, (size_t)slots);
 }
 
 static int grow_pool(vt_ctx *ctx, long long need) {
@@ -606,16 +627,19 @@ extern "C" int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int 
     VT_CHECK(ctx, cudaGetLastError());
     return 0;
 }
-extern "C" int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_ptrs, int n, uint32_t value) {
+extern "C" int vt_stream_signal_flags_on(vt_ctx *ctx, void *cuda_stream, uint32_t *const *host_ptrs, int n, uint32_t value) {
     if (!ctx || !host_ptrs || n < 1 || n > 16) return 1;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
     FlagTargets tg;
     memset(&tg, 0, sizeof tg);
     for (int k = 0; k < n; k++) tg.p[k] = host_ptrs[k];
-    signal_flags_kernel<<<1, 32, 0, ctx->stream>>>(tg, n, value);
+    signal_flags_kernel<<<1, 32, 0, cuda_stream ? (cudaStream_t)cuda_stream : ctx->stream>>>(tg, n, value);
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     return 0;
+}
+extern "C" int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_ptrs, int n, uint32_t value) {
+    return vt_stream_signal_flags_on(ctx, nullptr, host_ptrs, n, value);
 }
 extern "C" int vt_wait_status(vt_ctx *ctx, int *status) {
     if (!ctx || !status) return 1;

@@ -89,6 +89,39 @@ class FrameRenderer(StripeGather):
         torch.cuda.current_stream(self.cam.device).synchronize()
         return host_rgba8
 
+    # ---- pipelined variant (single GPU): the frame's device -> host copy overlaps the next frame's render ----------
+    def submit_frame(self, pos, rot, chunk_res, host_rgba8):
+        """Like frame_to_host but returns at once with a ticket; ``wait(ticket)`` blocks until ``host_rgba8`` holds
+        the frame.  Two device frames alternate, the copy runs on its own stream."""
+        assert self.world == 1, "the pipelined multi-GPU path is PeerFrameRenderer.submit_frame"
+        dev = self.cam.device
+        if not hasattr(self, "_pipe"):
+            self._pipe = dict(frames=[torch.zeros_like(self.frame) for _ in range(2)], copy=torch.cuda.Stream(dev),
+                              rendered=[torch.cuda.Event() for _ in range(2)], copied=[None, None], n=0)
+        p = self._pipe
+        b = p["n"] % 2
+        p["n"] += 1
+        main = torch.cuda.current_stream(dev)
+        self.cam.pos, self.cam.rot = pos, rot
+        if chunk_res is not None:
+            self.cam.set_chunk_res(chunk_res)
+        if p["copied"][b] is not None:
+            main.wait_event(p["copied"][b])                  # frame b was read out before it is rendered again
+        self.cam.render(stripes=(self.stripe, 1, 0), want=("rgba8",), prepare=True, out={"rgba8": p["frames"][b]})
+        p["rendered"][b].record(main)
+        p["copy"].wait_event(p["rendered"][b])
+        with torch.cuda.stream(p["copy"]):
+            host_rgba8.copy_(p["frames"][b], non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record(p["copy"])
+        p["copied"][b] = ev
+        return ev
+
+    @staticmethod
+    def wait(ticket):
+        if ticket is not None:
+            ticket.synchronize()
+
 
 # ------------------------------------------------------------------------------------------------------------
 # Frame assembly over NVLink peer memory: the render kernel itself delivers the pixels (no collective per frame).
@@ -208,6 +241,42 @@ class PeerFrameRenderer:
             self.release(b)
             torch.cuda.current_stream(self.cam.device).synchronize()
         return host_rgba8
+
+    # ---- pipelined variant: rank 0 reads frame b out on a copy stream while everybody renders frame b + 1 --------
+    def submit_frame(self, pos, rot, chunk_res, host_rgba8):
+        self.cam.pos, self.cam.rot = pos, rot
+        if chunk_res is not None:
+            self.cam.set_chunk_res(chunk_res)
+        dev = self.cam.device
+        if self.rank == 0 and not hasattr(self, "_pipe"):
+            self._pipe = dict(copy=torch.cuda.Stream(dev), copied=[None] * self.buffers)
+        if self.rank == 0:
+            b_next = self.frame_no % self.buffers
+            if self._pipe["copied"][b_next] is not None:     # rank 0 renders into it too: the read-out must be over
+                torch.cuda.current_stream(dev).wait_event(self._pipe["copied"][b_next])
+        b = self.render_frame(prepare=True)
+        if self.rank != 0:
+            return None
+        main, cp = torch.cuda.current_stream(dev), self._pipe["copy"]
+        ev_r = torch.cuda.Event()
+        ev_r.record(main)
+        cp.wait_event(ev_r)
+        C = self._C
+        with torch.cuda.stream(cp):
+            host_rgba8.copy_(self.frame_views[b], non_blocking=True)
+            if self.world > 1:                               # hand the buffer back once it has been read out
+                k = (self.frame_no - 1) // self.buffers + 1
+                arr = (C.c_void_p * (self.world - 1))(*[p + 4 * b for p in self.peer_credit[1:]])
+                self.cam._check(self.cam._lib.vt_stream_signal_flags_on(self.cam._ctx, C.c_void_p(cp.cuda_stream), arr, self.world - 1, k))
+            ev = torch.cuda.Event()
+            ev.record(cp)
+        self._pipe["copied"][b] = ev
+        return ev
+
+    @staticmethod
+    def wait(ticket):
+        if ticket is not None:
+            ticket.synchronize()
 
     def wait_status(self) -> int:
         C = self._C

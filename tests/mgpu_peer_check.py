@@ -40,6 +40,29 @@ def main():
             ok1, ok2 = torch.equal(single, host), torch.equal(single, host2)
             print("frame %d  peer==single %s  nccl==single %s" % (f, ok1, ok2), flush=True)
             bad += (not ok1) + (not ok2)
+    # pipelined: frame i is read out on the copy stream while frame i + 1 renders (bench.py's e2e loop)
+    n_pipe = 9
+    want = []
+    if rank == 0:
+        for f in range(n_pipe):
+            p = poses[f % len(poses)]
+            cam.pos, cam.rot = p["pos"], p["rot"]
+            cam.set_chunk_res(p["chunk_res"])
+            want.append(cam.render(want=("rgba8",))["rgba8"].cpu())
+    hosts = [host, host2]
+    prev = None
+    for f in range(n_pipe + 1):
+        tk = None
+        if f < n_pipe:
+            p = poses[f % len(poses)]
+            tk = peer.submit_frame(p["pos"], p["rot"], p["chunk_res"], hosts[f % 2])
+        if f > 0:
+            peer.wait(prev)
+            if rank == 0:
+                ok = torch.equal(want[f - 1], hosts[(f - 1) % 2])
+                print("pipelined frame %d == single %s" % (f - 1, ok), flush=True)
+                bad += not ok
+        prev = tk
     st = peer.wait_status()
     t = torch.tensor([bad + (st != 0)], device=dev)
     dist.all_reduce(t)
