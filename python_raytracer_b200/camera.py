@@ -76,7 +76,7 @@ class GpuCamera:
         self._settings_key = None
         self._frame_seed = 0
         self._visited = None
-        self._counters = torch.zeros(8, dtype=torch.int64, device=self.device)
+        self._counters = torch.zeros(16, dtype=torch.int64, device=self.device)
         self._pix_cache = {}
         self._static_materials = None
 

@@ -801,6 +801,7 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
     if (ctx->persist_blocks[which] == 0) {
         int nb = 0;
         VT_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, 128, 0));
+        if (getenv("VT_DEBUG")) fprintf(stderr, "voxtrace: persistent kernel %d: %d blocks/SM\n", which, nb);
         ctx->persist_blocks[which] = nb > 0 ? nb : 1;
     }
     long long want = (long long)((P.total_rays + 127) / 128);             // one ray slot per thread at least once

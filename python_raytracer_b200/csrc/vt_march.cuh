@@ -148,7 +148,10 @@ __device__ __forceinline__ bool rechunk(const DevParams &P, Lane &L, int ix, int
 // void step of init.py:114 (see vt_device.cuh void_step); for a power-of-two chunk size a / cs == a * (1 / cs) exactly
 template <bool FAST>
 __device__ __forceinline__ double void_step2(double px, double py, double pz, int radius, int cs, int cs_shift) {
-    double a = fmin(px, fmin(py, pz)) + i2d(radius);
+    // Python's min(): the first smallest argument; positions are never NaN, so two compares and selects do (fmin's
+    // NaN handling costs 8 instructions each on this target)
+    double a = pz < py ? pz : py;
+    a = (a < px ? a : px) + i2d(radius);
     double m;
     if (FAST || cs_shift >= 0) {
         double dcs = i2d(cs), inv = __hiloint2double((1023 - cs_shift) << 20, 0);
@@ -461,6 +464,9 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
 #ifndef VT_MARCH_KEEP
 #define VT_MARCH_KEEP 1             // the march phase goes on while >= KEEP/8 of the lanes that entered it still march
 #endif
+#ifndef VT_TRIPS           // dev instrumentation (tools/kbench.py KB_COUNTERS): phase trip counts in counters[8..13]
+#define VT_TRIPS 0
+#endif
 #ifndef VT_MINB
 #define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
 #endif
@@ -476,6 +482,9 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
     FirstHit fh; fh.hits = fh.fflag = fh.fx = fh.fy = fh.fz = 0; fh.first_step = -1.0;
     Counters c = {0, 0, 0, 0, 0, 0};
     unsigned rays = 0;
+#if VT_TRIPS
+    unsigned trips[6] = {0, 0, 0, 0, 0, 0};   // march trips, shade trips, shade lanes, refill trips, refill lanes, march phases
+#endif
     bool exhausted = false;                                                  // warp-uniform: the queue is empty
     for (;;) {
         const uint32_t state = lane_state(L);
@@ -486,6 +495,9 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
         if (nM + nH == 0 && nI == 0) break;
         if ((nI >= P.refill_min && nI > nM && nI > nH) || nM + nH == 0) {
             // ---- refill: finish ended rays, fetch new ray slots --------------------------------------------
+#if VT_TRIPS
+            if (COUNT && lane == 0) { trips[3]++; trips[4] += nI; }
+#endif
             if (state == ST_DONE) { finish_ray<FAST, REC>(P, L, fh); L.st = ST_NONE; }
             if (!exhausted) {
                 const unsigned need = __ballot_sync(full, lane_state(L) == ST_NONE);
@@ -500,11 +512,20 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
                 exhausted = base + (unsigned)cnt >= P.total_rays;
             }
         } else if (nH > nM) {
+#if VT_TRIPS
+            if (COUNT && lane == 0) { trips[1]++; trips[2] += nH; }
+#endif
             if (state == ST_HIT) shade_one<FAST, REC, COUNT>(P, L, fh, c);
         } else {
             // ---- march: iterate until too few lanes are still marching -------------------------------------
             const int thr = max(1, (nM * VT_MARCH_KEEP) >> 3);
+#if VT_TRIPS
+            if (COUNT && lane == 0) trips[5]++;
+#endif
             for (;;) {
+#if VT_TRIPS
+                if (COUNT && lane == 0) trips[0]++;
+#endif
                 int ix = 0, iy = 0, iz = 0, looked = 0;
                 bool leave = false;
                 if (lane_state(L) == ST_MARCH) {
@@ -526,6 +547,9 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
             unsigned t = __reduce_add_sync(full, v[k]);
             if (lane == 0 && t) atomicAdd(P.counters + k, (unsigned long long)t);
         }
+#if VT_TRIPS
+        if (lane == 0) for (int k = 0; k < 6; k++) atomicAdd(P.counters + 8 + k, (unsigned long long)trips[k]);
+#endif
     }
     // The last warp to leave resets the queue for the next launch and, with a frame target, publishes the arrival
     // flag: every thread's pixel stores are fenced at system scope first, so the peer that sees the flag sees the band.

@@ -57,6 +57,10 @@ def run_variant(spec, frames=8, settings=None, workload=None):
             cn = o2["counters"].cpu().numpy().astype(float)
             print("   pose counters per ray: samples_in %.2f void %.2f hits %.3f probes %.2f rechunk %.2f rays %d" %
                   (cn[1] / cn[0], cn[2] / cn[0], cn[3] / cn[0], cn[4] / cn[0], cn[5] / cn[0], int(cn[0])), flush=True)
+            if cn[8] > 0:                                # VT_TRIPS build: phase trips per 32 rays and lanes per trip
+                k = cn[0] / 32.0
+                print("   trips per 32 rays: march %.1f (lanes %.1f, %.1f phases) shade %.2f (lanes %.1f) refill %.2f (lanes %.1f)" %
+                      (cn[8] / k, (cn[1] + cn[2]) / cn[8], cn[13] / k, cn[9] / k, cn[10] / max(1, cn[9]), cn[11] / k, cn[12] / max(1, cn[11])), flush=True)
         sums.append(int(out["rgba8"].to(torch.int64).sum()))
     cam.close()
     print(json.dumps({"variant": spec, "ms_per_pose": [round(v, 3) for v in ms], "ms_mean": round(float(np.mean(ms)), 3),
