@@ -317,7 +317,8 @@ class GpuCamera:
         if "visited" in want:
             res["visited"] = self._visited
         if "counters" in want:
-            res["counters"] = self._counters
+            res["counters"] = self._counters[:8]
+            res["trips"] = self._counters[8:14]          # phase trip counts, only filled by a VT_TRIPS build (tools/kbench.py)
         return res
 
     def visited_slots(self, visited_bits) -> np.ndarray:

@@ -9,11 +9,13 @@ the global pixel index).  The visited-chunk mask is OR-reduced (as a max over u8
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 import torch
 import torch.distributed as dist
 
-STRIPE_ROWS = 8
+STRIPE_ROWS = int(os.environ.get("VT_STRIPE_ROWS", "8"))     # rows per interleaved stripe (tuning knob)
 
 
 def stripe_rows(height: int, rank: int, world: int, stripe: int = STRIPE_ROWS) -> np.ndarray:

@@ -70,3 +70,22 @@ def test_table_uploads_do_not_wait_for_the_frame_in_flight():
     got = cam.render(want=("rgba8",))["rgba8"]
     assert torch.equal(want, got)
     cam.close()
+
+
+def test_bench_line_contract():
+    """bench.py end to end on one GPU (short run): one JSON line with every key the measurement contract names."""
+    import json
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--steps", "4", "--warmup", "3"], capture_output=True,
+                       text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    for key in ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "higher_is_better", "scaling",
+                "vs_baseline", "dtype", "data", "config", "clocks", "e2e", "gpu_launches", "roofline", "cpu_baseline"):
+        assert key in line, key
+    assert line["steps"] == 4 and line["n_gpus"] == 1 and line["gpu_launches"] >= 4
+    assert line["value"] > 1e8 and line["e2e"]["value"] > 1e8 and line["e2e"]["d2h_bytes_per_step"] == 1920 * 1080 * 4
+    rf = line["roofline"]
+    assert rf["bound"] == "hbm" and 0 < rf["frac"] < 1 and abs(rf["frac"] - rf["achieved"] / rf["peak"]) < 1e-9
+    assert line["cpu_baseline"]["kind"] in ("port", "reference") and line["cpu_baseline"]["value"] > 0

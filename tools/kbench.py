@@ -57,6 +57,7 @@ def run_variant(spec, frames=8, settings=None, workload=None):
             cn = o2["counters"].cpu().numpy().astype(float)
             print("   pose counters per ray: samples_in %.2f void %.2f hits %.3f probes %.2f rechunk %.2f rays %d" %
                   (cn[1] / cn[0], cn[2] / cn[0], cn[3] / cn[0], cn[4] / cn[0], cn[5] / cn[0], int(cn[0])), flush=True)
+            cn = np.concatenate([cn, o2["trips"].cpu().numpy().astype(float), [0, 0]])
             if cn[8] > 0:                                # VT_TRIPS build: phase trips per 32 rays and lanes per trip
                 k = cn[0] / 32.0
                 print("   trips per 32 rays: march %.1f (lanes %.1f, %.1f phases) shade %.2f (lanes %.1f) refill %.2f (lanes %.1f)" %
