@@ -101,6 +101,12 @@ typedef struct {
  * cell = material of the LAST object in the list that has a voxel there (chunk frames are merged in object order,
  * later ones override, init.py:437-439).  Follow with vt_upload_dense(ctx, dev_cells).  One kernel launch. */
 int vt_build_world(vt_ctx *ctx, const vt_object *host_objects, int n, uint8_t *dev_cells);
+/* Objects whose `redraw` flag is set (init.py:397-404: their old and new chunks are rebuilt): redraws the cells of the
+ * box lo <= p < hi (absolute cells; clipped to the world, widened to whole bricks) of the same dense grid from the
+ * FULL object list in its current order, then updates the bricks of that box in place (new bricks take free slots,
+ * bricks that became empty release theirs).  The caller passes the union of the old and new chunk boxes of the
+ * objects that moved.  Three small launches and one host round trip, independent of the world size. */
+int vt_update_region(vt_ctx *ctx, const vt_object *host_objects, int n, uint8_t *dev_cells, const int32_t lo[3], const int32_t hi[3]);
 
 /* Goxel text model -> voxel list, the parser rules of Sprite.load (data.py:271-289): single-space separated
  * "x y z rrggbb" lines, non-numeric lines skipped, colours looked up in `keys` (n_keys strings; unknown ones are

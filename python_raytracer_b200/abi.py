@@ -14,7 +14,7 @@ RAY_RECORD = 16
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
            "vt_set_settings", "vt_set_materials", "vt_set_camera", "vt_set_world", "vt_set_chunk_table",
            "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
-           "vt_launch_count", "vt_build_world", "vt_goxel_parse", "vt_free",
+           "vt_launch_count", "vt_build_world", "vt_update_region", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
            "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
 
@@ -84,6 +84,7 @@ def load(path: str | None = None):
         "vt_region_pixels": (i64, [C.POINTER(VtRegion)]),
         "vt_launch_count": (i64, [vp]),
         "vt_build_world": (C.c_int, [vp, C.POINTER(VtObject), i32, vp]),
+        "vt_update_region": (C.c_int, [vp, C.POINTER(VtObject), i32, vp, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
         "vt_goxel_parse": (C.c_int, [C.c_char_p, C.c_int32, C.POINTER(C.c_char_p), i32, C.POINTER(C.POINTER(C.c_int32)),
                                      C.POINTER(C.POINTER(C.c_uint8)), C.POINTER(i64), C.c_char_p, i32]),
         "vt_free": (None, [vp]),

@@ -185,6 +185,60 @@ __global__ void build_world_kernel(const vt_object *__restrict__ objs, int n, in
     }
 }
 
+// Same for the cells of a box [lo, lo + ext) of the grid only (dirty chunks of objects that moved).
+__global__ void build_region_kernel(const vt_object *__restrict__ objs, int n, int ox, int oy, int oz, int ny, int nz,
+                                    int lx0, int ly0, int lz0, int ex, int ey, int ez, uint8_t *__restrict__ cells) {
+    const long long total = (long long)ex * ey * ez;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+        const int x = lx0 + (int)(i / ((long long)ez * ey)), y = ly0 + (int)((i / ez) % ey), z = lz0 + (int)(i % ez);
+        const int wx = x + ox, wy = y + oy, wz = z + oz;
+        uint8_t m = 0;
+        for (int k = n - 1; k >= 0 && !m; k--) {
+            const vt_object &o = objs[k];
+            if (wx < o.mins[0] || wx >= o.maxs[0] || wy < o.mins[1] || wy >= o.maxs[1] || wz < o.mins[2] || wz >= o.maxs[2]) continue;
+            int lx = wx - o.mins[0], ly = wy - o.mins[1], lz = wz - o.mins[2];
+            pos_rotated(o, lx, ly, lz);
+            if ((unsigned)lx >= (unsigned)o.size[0] || (unsigned)ly >= (unsigned)o.size[1] || (unsigned)lz >= (unsigned)o.size[2]) continue;
+            m = o.dev_sprite[((size_t)lx * o.size[1] + ly) * o.size[2] + lz];
+        }
+        cells[((size_t)x * ny + y) * nz + z] = m;
+    }
+}
+
+// one warp per brick of the box of bricks [b0, b0 + nbr): flags[i] = brick holds a voxel
+__global__ void region_flags_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int bx0, int by0, int bz0,
+                                    int rbx, int rby, int rbz, uint8_t *flags) {
+    const int warps = (gridDim.x * blockDim.x) >> 5, lane = threadIdx.x & 31;
+    const int total = rbx * rby * rbz;
+    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
+        const int bz = bz0 + i % rbz, by = by0 + (i / rbz) % rby, bx = bx0 + i / (rbz * rby);
+        unsigned any = 0;
+        for (int t = lane; t < 512; t += 32) {
+            const int x = bx * 8 + (t >> 6), y = by * 8 + ((t >> 3) & 7), z = bz * 8 + (t & 7);
+            if (x < nx && y < ny && z < nz) any |= dense[((size_t)x * ny + y) * nz + z];
+        }
+        any = __any_sync(0xffffffffu, any != 0);
+        if (lane == 0) flags[i] = (uint8_t)any;
+    }
+}
+
+// copy the region's non-empty bricks from the dense grid into their pool slots and patch the brick table
+// (one block of 512 threads per brick; slot 0xffffffff = brick became empty)
+__global__ void region_fill_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nby, int nbz, int bx0, int by0,
+                                   int bz0, int rby, int rbz, const uint32_t *__restrict__ slots, int m, uint8_t *pool,
+                                   uint32_t *brick_tab) {
+    for (int i = blockIdx.x; i < m; i += gridDim.x) {
+        const int bz = bz0 + i % rbz, by = by0 + (i / rbz) % rby, bx = bx0 + i / (rbz * rby);
+        const uint32_t slot = slots[i];
+        const int t = threadIdx.x;
+        if (slot != 0xffffffffu) {
+            const int x = bx * 8 + (t >> 6), y = by * 8 + ((t >> 3) & 7), z = bz * 8 + (t & 7);
+            pool[(size_t)slot * 512 + t] = (x < nx && y < ny && z < nz) ? dense[((size_t)x * ny + y) * nz + z] : 0;
+        }
+        if (t == 0) brick_tab[((size_t)bx * nby + by) * nbz + bz] = slot == 0xffffffffu ? 0u : slot + 1u;
+    }
+}
+
 // Peer-memory handshakes of the multi-GPU frame path.  Flags are u32 words in cudaMalloc'ed memory
 // that peers reach through CUDA IPC; values only grow (frame sequence numbers), so a waiter never misses one.
 __global__ void wait_flags_kernel(const unsigned int *flags, int n, unsigned int value, long long timeout_cycles, int *status) {
@@ -562,6 +616,83 @@ extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t
     VT_CHECK(ctx, cudaGetLastError());
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     cudaFree(d_objs);
+    return 0;
+}
+
+// Objects that moved: redraw the cells of the chunk-aligned box [lo, hi) (absolute cells, clipped to the world) from
+// the whole object list, then bring the bricks of that box up to date -- flags on the device, slot assignment on the
+// host (free list), fill + table patch on the device.  Cost scales with the box, not with the world.
+extern "C" int vt_update_region(vt_ctx *ctx, const vt_object *objs, int n, uint8_t *dev_cells, const int32_t lo[3], const int32_t hi[3]) {
+    if (!ctx || !dev_cells || !lo || !hi || n < 0 || (n && !objs)) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_update_region: no world (vt_set_world)");
+    for (int k = 0; k < n; k++) {
+        if (!objs[k].dev_sprite) return fail(ctx, "vt_update_region: object without a sprite grid");
+        for (int a = 0; a < 3; a++) {
+            if (objs[k].size[a] <= 0) return fail(ctx, "vt_update_region: sprite size must be positive");
+            if (objs[k].angle[a] < 0 || objs[k].angle[a] > 3) return fail(ctx, "vt_update_region: angle must be 0..3");
+        }
+    }
+    int l[3], e[3], b0[3], rb[3];
+    for (int a = 0; a < 3; a++) {
+        long long p = (long long)lo[a] - ctx->origin[a], q = (long long)hi[a] - ctx->origin[a];
+        if (p < 0) p = 0;
+        if (q > ctx->dims[a]) q = ctx->dims[a];
+        if (q <= p) return 0;                                  // nothing of the box lies inside the world
+        p = (p / VT_BRICK) * VT_BRICK;                         // whole bricks
+        q = ((q + VT_BRICK - 1) / VT_BRICK) * VT_BRICK;
+        if (q > ctx->dims[a]) q = ctx->dims[a];
+        l[a] = (int)p; e[a] = (int)(q - p);
+        b0[a] = (int)(p / VT_BRICK); rb[a] = (int)((q - p + VT_BRICK - 1) / VT_BRICK);
+    }
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const int m = rb[0] * rb[1] * rb[2];
+    vt_object *d_objs = nullptr;
+    uint8_t *d_flags = nullptr;
+    uint32_t *d_slots = nullptr;
+    if (n) {
+        VT_CHECK(ctx, cudaMalloc(&d_objs, (size_t)n * sizeof(vt_object)));
+        VT_CHECK(ctx, cudaMemcpyAsync(d_objs, objs, (size_t)n * sizeof(vt_object), cudaMemcpyHostToDevice, ctx->stream));
+    }
+    VT_CHECK(ctx, cudaMalloc(&d_flags, (size_t)m));
+    VT_CHECK(ctx, cudaMalloc(&d_slots, (size_t)m * sizeof(uint32_t)));
+    const long long total = (long long)e[0] * e[1] * e[2];
+    long long want = (total + 255) / 256;
+    build_region_kernel<<<(int)(want < 148LL * 32 ? want : 148LL * 32), 256, 0, ctx->stream>>>(
+        d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[1], ctx->dims[2], l[0], l[1], l[2], e[0], e[1], e[2], dev_cells);
+    region_flags_kernel<<<(m + 3) / 4 < 148 * 16 ? (m + 3) / 4 : 148 * 16, 128, 0, ctx->stream>>>(
+        dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], b0[0], b0[1], b0[2], rb[0], rb[1], rb[2], d_flags);
+    ctx->launches += 2;
+    VT_CHECK(ctx, cudaGetLastError());
+    std::vector<uint8_t> flags((size_t)m);
+    VT_CHECK(ctx, cudaMemcpyAsync(flags.data(), d_flags, (size_t)m, cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    std::vector<uint32_t> slots((size_t)m);
+    long long need = ctx->pool_used;
+    for (int i = 0; i < m; i++) {
+        const int bz = b0[2] + i % rb[2], by = b0[1] + (i / rb[2]) % rb[1], bx = b0[0] + i / (rb[2] * rb[1]);
+        const size_t ti = ((size_t)bx * ctx->nb[1] + by) * ctx->nb[2] + bz;
+        const uint32_t cur = ctx->h_brick_tab[ti];
+        if (!flags[(size_t)i]) {
+            if (cur) ctx->free_slots.push_back(cur - 1);
+            slots[(size_t)i] = 0xffffffffu; ctx->h_brick_tab[ti] = 0;
+        } else {
+            uint32_t slot;
+            if (cur) slot = cur - 1;
+            else if (!ctx->free_slots.empty()) { slot = ctx->free_slots.back(); ctx->free_slots.pop_back(); }
+            else slot = (uint32_t)need++;
+            slots[(size_t)i] = slot; ctx->h_brick_tab[ti] = slot + 1;
+        }
+    }
+    if (int rc = grow_pool(ctx, need)) return rc;
+    ctx->pool_used = need;
+    VT_CHECK(ctx, cudaMemcpyAsync(d_slots, slots.data(), (size_t)m * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
+    region_fill_kernel<<<m < 148 * 8 ? m : 148 * 8, 512, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1],
+                                                                     ctx->nb[2], b0[0], b0[1], b0[2], rb[1], rb[2], d_slots, m,
+                                                                     ctx->d_pool, ctx->d_brick_tab);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    cudaFree(d_objs); cudaFree(d_flags); cudaFree(d_slots);
     return 0;
 }
 

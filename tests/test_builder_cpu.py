@@ -47,3 +47,22 @@ def test_scene_from_reference_objects():
     for k, o in enumerate(scene):
         assert np.array_equal(o.sprite, objs["sprite_%d" % k])
         assert list(o.pos) == objs["pos_%d" % k].tolist() and list(o.rot) == objs["rot_%d" % k].tolist()
+
+
+def test_chunk_box_matches_reference_chunk_loop():
+    """chunk_box = the chunks Window.chunk_update loops over for an object (init.py:406-411: mins.snapped ..
+    maxs.snapped inclusive), checked on the object states the reference recorded in default_moves.npz."""
+    import os
+    import numpy as np
+    from python_raytracer_b200.builder import SceneObject, chunk_box
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    objs, mv = np.load(os.path.join(gold, "default_objects.npz")), np.load(os.path.join(gold, "default_moves.npz"))
+    for s in range(int(mv["steps"])):
+        st = mv["state_%d" % s]
+        for k in range(int(mv["count"])):
+            o = SceneObject(sprite=objs["sprite_%d" % k], pos=tuple(st[k, 1:4]), rot=tuple(st[k, 4:7]))
+            mins, maxs = o.box()
+            lo, hi = chunk_box(o, 16)
+            for a in range(3):
+                assert lo[a] % 16 == 0 and hi[a] % 16 == 0
+                assert lo[a] <= mins[a] < lo[a] + 16 and hi[a] - 16 <= maxs[a] < hi[a]

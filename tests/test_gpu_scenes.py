@@ -220,3 +220,64 @@ def test_c5_goxel_model_culling_full_size(tmp_path):
     cells_np = cells.cpu().numpy()
     _check_against_oracle(cam, sd, wb.origin.astype(np.int32), cells_np, res, C5_MATERIALS, pos, rot, px, frames[3])
     cam.close()
+
+
+# ------------------------------------------------------------------------------------------------ incremental updates
+def _embed(cells, origin, lo, hi):
+    out = np.zeros(tuple(int(v) for v in (hi - lo)), np.uint8)
+    o = (np.asarray(origin, np.int64) - lo).astype(int)
+    s = cells.shape
+    out[o[0]:o[0] + s[0], o[1]:o[1] + s[1], o[2]:o[2] + s[2]] = cells
+    return out
+
+
+def test_builder_update_follows_reference_chunk_update():
+    """tests/golden/default_moves.npz: the reference's chunk_update run six times while objects move into each other,
+    turn, get removed and leave the initial box.  WorldBuilder.update must leave the same merged world after every
+    step (dirty chunks only, override order = re-insertion order), and the bricked world must render like a world
+    built from scratch from the same cells."""
+    from python_raytracer_b200.builder import SceneObject, WorldBuilder
+    objs = np.load(os.path.join(GOLD, "default_objects.npz"))
+    world = np.load(os.path.join(GOLD, "default_world.npz"))
+    mv = np.load(os.path.join(GOLD, "default_moves.npz"))
+    n = int(mv["count"])
+    assert n == int(objs["count"])
+    cam = _camera(dict(width=96, height=64, chunk_size=16, chunk_lod=0, dist_max=192, samples=1, max_bounces=2, static=True))
+    cam.pos = (-12.0, 4.0, 4.0)
+    wb = WorldBuilder(cam)
+    scene = [SceneObject(sprite=objs["sprite_%d" % k]) for k in range(n)]
+    full_rebuilds = 0
+    for s in range(int(mv["steps"])):
+        st = mv["state_%d" % s]
+        live, redraw = [], []
+        for k, o in enumerate(scene):
+            present, dirty = bool(st[k, 0]), bool(st[k, 8])
+            o.pos, o.rot, o.visible = tuple(st[k, 1:4]), tuple(st[k, 4:7]), bool(st[k, 7])
+            if present:
+                live.append(o)
+            if dirty or (not present and id(o) in wb.drawn):
+                redraw.append(o)
+        if s == 0:
+            wb.build(live, world["materials"], margin=1)
+        else:
+            before = wb.cells.data_ptr()
+            wb.update(live, redraw)
+            full_rebuilds += wb.cells.data_ptr() != before
+        got, want = wb.cells.cpu().numpy(), mv["cells_%d" % s]
+        lo = np.minimum(wb.origin, mv["origin_%d" % s].astype(np.int64))
+        hi = np.maximum(wb.origin + np.array(got.shape), mv["origin_%d" % s].astype(np.int64) + np.array(want.shape))
+        a, b = _embed(got, wb.origin, lo, hi), _embed(want, mv["origin_%d" % s], lo, hi)
+        assert np.array_equal(a, b), "step %d: %d cells differ" % (s, int((a != b).sum()))
+        # the incrementally patched bricks render like bricks made from scratch out of the same cells
+        cam2 = _camera(dict(width=96, height=64, chunk_size=16, chunk_lod=0, dist_max=192, samples=1, max_bounces=2, static=True))
+        cam2.pos = cam.pos
+        from python_raytracer_b200.world import lod_table
+        res = lod_table(wb.origin, wb.present, list(cam.pos), 16, 0, 192)
+        cam2.set_world_dense(wb.origin, got, res, world["materials"])
+        wb.update_lod()
+        frame = cam.render(want=("rgba8",))["rgba8"].cpu().numpy()
+        frame2 = cam2.render(want=("rgba8",))["rgba8"].cpu().numpy()
+        assert np.array_equal(frame, frame2), "step %d: patched bricks render differently" % s
+        cam2.close()
+    assert full_rebuilds == 1                     # only the step that leaves the box rebuilds everything
+    cam.close()

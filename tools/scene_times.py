@@ -77,5 +77,16 @@ res["c5"] = dict(voxels=int(len(xyz)), file_mb=round(os.path.getsize(path) / 1e6
                  grid_s=round(t3 - t2, 3), build_and_brick_s=round(t5 - t4, 4), ms_all_chunks=round(ms_all, 3), ms_culled=round(ms_cull, 3),
                  chunks_all=int((res_all > 0).sum()), chunks_culled=int((res_c > 0).sum()), rays=int(cnt[0]),
                  grays_per_s=round(cnt[0] / ms_cull / 1e6, 3), bricks=cam.world_stats()["bricks"])
+# ---- a small object moving through the C5 world: incremental update (dirty chunks only) vs full rebuild
+cube = SceneObject(sprite=np.full((16, 16, 16), 2, np.uint8), pos=(40.0, 150.0, 40.0))
+wb.build([obj, cube], C5_MATERIALS, margin=1); torch.cuda.synchronize()
+ups = []
+for k in range(20):
+    cube.pos = (40.0 + 3.0 * k, 150.0, 40.0 + 2.0 * k)
+    torch.cuda.synchronize(); t0 = time.perf_counter()
+    n_chunks = wb.update([obj, cube], [cube]); torch.cuda.synchronize()
+    ups.append(time.perf_counter() - t0)
+t0 = time.perf_counter(); wb.build([obj, cube], C5_MATERIALS, margin=1); torch.cuda.synchronize(); t_full = time.perf_counter() - t0
+res["c5_moving_object"] = dict(update_ms=round(1e3 * float(np.median(ups)), 3), chunks_redrawn=int(n_chunks), full_rebuild_ms=round(1e3 * t_full, 2))
 os.remove(path)
 print(json.dumps(res, indent=1))
