@@ -223,6 +223,8 @@ def run_ours(args, rank, world, local_rank):
     t_total, t_kernel = float(tt[0]), float(tt[1])
     ms_step = t_total / args.steps
     value = rays_frame / (ms_step * 1e-3)
+    per_frame = sorted(a.elapsed_time(c) for a, _, c in ev)             # this rank's frames (rank 0 is the one that prints)
+    ms_median, ms_p95 = per_frame[len(per_frame) // 2], per_frame[min(len(per_frame) - 1, int(0.95 * len(per_frame)))]
 
     # ---- end to end through the public API with host buffers ------------------------------------------------
     # Every step: camera + LOD table + materials host -> device, render, assembly, frame device -> host into pinned
@@ -273,21 +275,23 @@ def run_ours(args, rank, world, local_rank):
     except Exception:
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
-    traffic, traffic_src = None, None
+    traffic, traffic_src, ncu_side = None, None, None
     try:          # dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture
         tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
         traffic, traffic_src = float(tj["traffic_bytes_per_launch_mean"]), tj["source"]
+        # what actually bounds this kernel (same capture; profiler numbers, reported beside the roofline, not timed here)
+        ncu_side = {k: [round(float(v), 2) for v in tj[k]] for k in ("issue_active_pct", "lanes_per_instruction", "l1_hit_pct", "l2_hit_pct") if k in tj}
     except Exception:
-        pass
+        ncu_side = None
     achieved = alg_bytes / (t_kernel * 1e-3) / 1e9
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "traffic_source": traffic_src, "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback 6650",
                 "kernel": "render_persistent", "kernel_ms_per_launch": t_kernel / args.steps,
-                "alg_bytes_per_launch": alg_bytes / args.steps,
+                "alg_bytes_per_launch": alg_bytes / args.steps, "ncu_per_pose": ncu_side,
                 "per_ray": {k: float(cnt_tot[j]) / max(1, cnt_tot[0]) for j, k in
                             enumerate(["rays", "in_chunk_samples", "void_samples", "hits", "neighbour_probes", "chunk_reevals", "iterations"])}}
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "frames_per_sec": 1000.0 / ms_step, "higher_is_better": True, "scaling": "strong",
+            "ms_per_step": ms_step, "ms_median": ms_median, "ms_p95": ms_p95, "frames_per_sec": 1000.0 / ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world, use_peer),
             "clocks": clocks, "gpu_launches": int(launches),
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": 1000.0 * float(te[0]) / args.steps,

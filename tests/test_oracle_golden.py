@@ -24,3 +24,21 @@ def test_oracle_matches_reference(name):
     # fp64 results: libm pow/sin may pick CPU-specific code paths (glibc ifunc), so allow 1e-12 but expect 0
     np.testing.assert_allclose(o["ray0"], c["ray0"], rtol=1e-12, atol=1e-12)
     assert np.array_equal(o["visited"], c["visited"])
+
+
+def test_survey_known_answers():
+    """SURVEY.md §8c lists values read off the reference while the survey was written (default mod as shipped, camera
+    (-12, 4, 4), rot 0, culling off, static): the golden made later by oracle/gen_golden.py and the C oracle must
+    both hold them."""
+    c = load_case("c1_shipped")
+    world = cport.World(c["origin"], c["cells"], c["chunk_res"], c["materials"])
+    o = cport.render(c["settings"], c["cam_pos"], c["cam_rot"], float(c["cam_lens"]), world, pixels=c["pixels"],
+                     rng=cport.RNG_MT19937)
+    px = c["pixels"]
+    for (x, y), rgba, first in (((32, 24), (21, 21, 21, 109), None), ((0, 0), (74, 84, 94, 212), (-9, 7, 8)),
+                                ((63, 47), (22, 22, 22, 109), None)):
+        i = int(np.nonzero((px[:, 0] == x) & (px[:, 1] == y))[0][0])
+        for src in (c, o):
+            assert tuple(int(v) for v in src["mean"][i]) == rgba, (x, y)
+            if first is not None:
+                assert tuple(int(v) for v in src["ray0"][i, 7:10]) == first and int(src["ray0"][i, 11]) == 7
