@@ -362,5 +362,15 @@ class GpuCamera:
             out = self.render(pixels=px, want=("rgba8", "visited"), prepare=False)
             frame = torch.zeros((int(s.height), int(s.width), 4), dtype=torch.uint8, device=self.device)
             frame[px[:, 1].long(), px[:, 0].long()] = out["rgba8"]
-        image = frame.cpu().numpy().tobytes()
-        return image, self.traversed(out["visited"]), thread
+        # device -> host through pinned staging buffers (frame and visited bits in flight together), then the one
+        # copy `bytes` needs: pg.image.frombytes wants a real bytes object (init.py:186)
+        key = (tuple(frame.shape), int(out["visited"].numel()))
+        if getattr(self, "_tile_stage", (None,))[0] != key:
+            self._tile_stage = (key, torch.empty(frame.shape, dtype=torch.uint8).pin_memory(),
+                                torch.empty(out["visited"].shape, dtype=out["visited"].dtype).pin_memory())
+        _, h_frame, h_vis = self._tile_stage
+        h_frame.copy_(frame, non_blocking=True)
+        h_vis.copy_(out["visited"], non_blocking=True)
+        torch.cuda.current_stream(self.device).synchronize()
+        image = h_frame.numpy().tobytes()
+        return image, self.traversed(h_vis), thread
