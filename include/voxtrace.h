@@ -56,6 +56,9 @@ int vt_create(int device, vt_ctx **out);
 void vt_destroy(vt_ctx *ctx);
 const char *vt_last_error(const vt_ctx *ctx);   /* ctx may be NULL: error of the last failed vt_create */
 int vt_abi_version(void);
+/* Build variant of the loaded library: bit 0 = bounds-checked kernels (-DVT_CHECKED=1, tests/check_bounds.sh),
+ * bit 1 = phase-trip instrumentation (-DVT_TRIPS=1, tools/kbench.py).  0 for the product build. */
+int vt_build_flags(void);
 /* Use an existing CUDA stream (cudaStream_t, e.g. torch's current stream) instead of the context's own. */
 int vt_set_stream(vt_ctx *ctx, void *cuda_stream);
 int vt_sync(vt_ctx *ctx);

@@ -14,7 +14,7 @@ RAY_RECORD = 16
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
            "vt_set_settings", "vt_set_materials", "vt_set_camera", "vt_set_world", "vt_set_chunk_table",
            "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
-           "vt_launch_count", "vt_build_world", "vt_update_region", "vt_goxel_parse", "vt_free",
+           "vt_launch_count", "vt_build_flags", "vt_build_world", "vt_update_region", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
            "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
 
@@ -57,6 +57,7 @@ def load(path: str | None = None):
     global _lib
     if _lib is not None and path is None:
         return _lib
+    path = path or os.environ.get("VT_LIB") or None       # VT_LIB: a tuning / checked build (tools/build_variants.py)
     p = path or _build.LIB_PATH
     if path is None and _build.needs_build():
         _build.build_library()
@@ -70,6 +71,7 @@ def load(path: str | None = None):
         "vt_destroy": (None, [vp]),
         "vt_last_error": (C.c_char_p, [vp]),
         "vt_abi_version": (C.c_int, []),
+        "vt_build_flags": (C.c_int, []),
         "vt_set_stream": (C.c_int, [vp, vp]),
         "vt_sync": (C.c_int, [vp]),
         "vt_set_settings": (C.c_int, [vp, C.POINTER(VtSettings)]),

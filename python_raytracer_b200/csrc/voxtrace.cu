@@ -384,6 +384,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     delete ctx;
 }
 
+extern "C" int vt_build_flags(void) { return (VT_CHECKED ? 1 : 0) | (VT_TRIPS ? 2 : 0); }
 extern "C" const char *vt_last_error(const vt_ctx *ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
 extern "C" int64_t vt_launch_count(const vt_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
@@ -941,6 +942,20 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
     if (grid < 1) grid = 1;
     P.total_warps = (unsigned)grid * 4u;
     fn<<<grid, 128, 0, ctx->stream>>>(P, ctx->d_row_y);
+#if VT_CHECKED
+    {
+        unsigned code = 0;
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        VT_CHECK(ctx, cudaMemcpyFromSymbol(&code, vt_oob_code, sizeof code));
+        if (code) {
+            unsigned zero = 0;
+            cudaMemcpyToSymbol(vt_oob_code, &zero, sizeof zero);
+            char msg[96];
+            snprintf(msg, sizeof msg, "vt_render: bounds check failed in the render kernel, site %u", code);
+            return fail(ctx, msg);
+        }
+    }
+#endif
     return 0;
 }
 
@@ -962,6 +977,7 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
     w.nbx = ctx->nb[0]; w.nby = ctx->nb[1]; w.nbz = ctx->nb[2];
     w.ncx = ctx->nc[0]; w.ncy = ctx->nc[1]; w.ncz = ctx->nc[2];
     w.brick_tab = ctx->d_brick_tab; w.pool = ctx->d_pool; w.chunk_res = ctx->d_chunk_res; w.mats = ctx->d_mats;
+    w.pool_slots = (unsigned)ctx->pool_used;
     memcpy(P.cam.pos, ctx->cam_pos, sizeof P.cam.pos);
     memcpy(P.cam.rot, ctx->cam_rot, sizeof P.cam.rot);
     P.cam.lens = ctx->cam_lens;

@@ -27,7 +27,20 @@ struct DevWorld {
     const uint8_t *pool;            // [slots][512]     material ids, (lx*8 + ly)*8 + lz
     const uint8_t *chunk_res;       // [ncx][ncy][ncz]  0 = no frame, else Frame.resolution
     const double *mats;             // [256][8]         vt_material rows
+    unsigned int pool_slots;        // bricks held by the pool (bound for the checked build)
 };
+
+// Checked build (-DVT_CHECKED=1, tests/check_bounds.sh): every table index of the render kernel is tested against the
+// table's size; a violation records its site code and the access is skipped.  vt_render then fails with that code.
+#ifndef VT_CHECKED
+#define VT_CHECKED 0
+#endif
+#if VT_CHECKED
+__device__ unsigned int vt_oob_code = 0;
+#define VT_IN(cond, code) ((cond) ? true : (atomicMax(&vt_oob_code, (unsigned)(code)), false))
+#else
+#define VT_IN(cond, code) true
+#endif
 
 struct DevCamera {
     double pos[3];
@@ -256,6 +269,7 @@ __device__ __forceinline__ void mark_visited(uint32_t *visited, int slot) {
     if (!visited) return;
     uint32_t bit = 1u << (slot & 31);
     uint32_t *word = visited + (slot >> 5);
+    if (!VT_IN(slot >= 0, 10)) return;
     if (!(*(volatile uint32_t *)word & bit)) atomicOr(word, bit);
 }
 

@@ -93,8 +93,9 @@ __device__ __forceinline__ int lod_snap(const DevParams &P, int res, int r, int 
 }
 
 __device__ __forceinline__ int cell_at(const DevWorld &w, int qx, int qy, int qz) {
+    if (!VT_IN((unsigned)(qx >> 3) < (unsigned)w.nbx && (unsigned)(qy >> 3) < (unsigned)w.nby && (unsigned)(qz >> 3) < (unsigned)w.nbz, 1)) return 0;
     uint32_t b = __ldg(&w.brick_tab[((qx >> 3) * w.nby + (qy >> 3)) * w.nbz + (qz >> 3)]);
-    if (b == 0u) return 0;
+    if (b == 0u || !VT_IN(b <= w.pool_slots, 2)) return 0;
     return __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
 }
 
@@ -136,7 +137,7 @@ __device__ __forceinline__ bool rechunk(const DevParams &P, Lane &L, int ix, int
     int slot = chunk_slot_rel<FAST>(w, cs, sh, L.cx, L.cy, L.cz);
     L.res = 0;
     if (COUNT) c.rechunk++;
-    if (slot >= 0) { L.res = __ldg(&w.chunk_res[slot]); mark_visited(P.visited, slot); }
+    if (slot >= 0 && VT_IN(slot < w.ncx * w.ncy * w.ncz, 3)) { L.res = __ldg(&w.chunk_res[slot]); mark_visited(P.visited, slot); }
     else if (!FULL_TAIL) {
         bool gone = (ix >= w.nx && L.vx >= 0.0) || (ix < 0 && L.vx <= 0.0) || (iy >= w.ny && L.vy >= 0.0) ||
                     (iy < 0 && L.vy <= 0.0) || (iz >= w.nz && L.vz >= 0.0) || (iz < 0 && L.vz <= 0.0);
@@ -208,9 +209,9 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
                 qx = lod_snap<FAST>(P, L.res, ix, 0); qy = lod_snap<FAST>(P, L.res, iy, 1); qz = lod_snap<FAST>(P, L.res, iz, 2);
                 in = qx >= L.cx && qy >= L.cy && qz >= L.cz;            // q <= i, so only the near faces can fail
             }
-            if (in) {
+            if (in && VT_IN((unsigned)(qx >> 3) < (unsigned)w.nbx && (unsigned)(qy >> 3) < (unsigned)w.nby && (unsigned)(qz >> 3) < (unsigned)w.nbz, 4)) {
                 const uint32_t b = __ldg(&w.brick_tab[((qx >> 3) * w.nby + (qy >> 3)) * w.nbz + (qz >> 3)]);
-                if (b) mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
+                if (b && VT_IN(b <= w.pool_slots, 5)) mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
                 else if (L.res == 1 && P.brick_runs) {
                     for (;;) {
                         L.step += 1.0;
@@ -297,7 +298,7 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
             } else {                                                         // Camera.chunk_get, init.py:28-33
                 int nx = snap_rel<FAST>(jx_, cs, sh), ny = snap_rel<FAST>(jy_, cs, sh), nz = snap_rel<FAST>(jz_, cs, sh);
                 int nslot = chunk_slot_rel<FAST>(w, cs, sh, nx, ny, nz);
-                int nres = nslot >= 0 ? (int)__ldg(&w.chunk_res[nslot]) : 0;
+                int nres = (nslot >= 0 && VT_IN(nslot < w.ncx * w.ncy * w.ncz, 6)) ? (int)__ldg(&w.chunk_res[nslot]) : 0;
                 if (nres) { nid = lookup_any<FAST>(P, nx, ny, nz, nres, jx_, jy_, jz_); if (COUNT) c.probes++; }
             }
             flip[k] = (nid == 0) || (__ldg(w.mats + 8 * nid + 5) != ior);
@@ -313,6 +314,7 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
 // init.py:131-134: samples traced for pixel (x, y); dir_x / dir_y come from host tables (exact divisions)
 __device__ __forceinline__ int pixel_samples(const DevParams &P, int x, int y, double &dir_x, double &dir_y, double &detail) {
     const vt_settings &s = P.s;
+    if (!VT_IN((unsigned)x < (unsigned)s.width && (unsigned)y < (unsigned)s.height, 7)) { dir_x = dir_y = 0.0; detail = 1.0; return 1; }
     dir_x = __ldg(P.cam.dir_x + x);
     dir_y = __ldg(P.cam.dir_y + y);
     if (s.lod_edge == 0.0) { detail = 1.0; return s.samples < 1 ? 1 : s.samples; }
@@ -345,6 +347,7 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
     double dx_, dy_, det_;
     const int n = pixel_samples(P, x, y, dx_, dy_, det_);
     const size_t i = L.out_i;
+    if (!VT_IN((long long)i < P.n_pixels, 8)) return;
     if (REC && lane_sample(L) == 0u) {
         double *o = P.ray0 + (size_t)VT_RAY_RECORD * i;
         o[0] = cr; o[1] = cg; o[2] = cb; o[3] = L.energy; o[4] = L.bounces; o[5] = L.step;
@@ -389,6 +392,7 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
             // frame target (multi-GPU): the pixel goes straight to its place in the full frame, which may live on a
             // peer GPU (NVLink store), instead of this rank's compact band
             const size_t o = P.frame_target ? (size_t)y * (size_t)s.width + (size_t)x : i;
+            if (!VT_IN(!P.frame_target || o < (size_t)s.width * (size_t)s.height, 9)) return;
             reinterpret_cast<uchar4 *>(P.frame_target ? P.frame_target : P.rgba8)[o] = q;
         }
     }
@@ -417,7 +421,7 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
         int lx = pi & (P.tile_w - 1), ly = pi >> P.tile_w_shift;
         int col = (int)tx * P.tile_w + lx, lr = (int)ty * P.tile_h + ly;
         pv = col < bw && lr < P.band_rows;
-        if (pv) { x = P.x0 + col; y = __ldg(row_y + lr); L.out_i = (uint32_t)(lr * bw + col); }
+        if (pv && VT_IN(lr >= 0 && col >= 0, 11)) { x = P.x0 + col; y = __ldg(row_y + lr); L.out_i = (uint32_t)(lr * bw + col); }
     }
     if (!pv) return;
     double dir_x, dir_y, detail;
