@@ -191,10 +191,8 @@ __device__ __forceinline__ int march_leave_chunk(const DevParams &P, Lane &L, Co
 // Block B (init.py:75-77, 114-116): examine the cell under the ray; a solid one turns the lane into HIT (the position
 // is not advanced -- the material phase does that), an empty one advances the ray.
 //
-// Empty-brick run: when the cell's 8^3 brick holds no voxel at all, every further sample that still falls into the
-// same brick is known to be empty and inside the same chunk (bricks never straddle chunks when chunk_size % 8 == 0),
-// so those samples only need the position update and the floor -- the sample positions themselves are the
-// reference's, one fp64 add per axis per sample.  This is what shortens the long rays of a packet.
+// Brick-local loop: in a full-resolution chunk the lane then stays in a tight loop for as long as its samples fall into
+// the same 8^3 brick (see below) -- this is what shortens the long rays a packet waits for.
 template <bool FAST, bool COUNT>
 __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters &c, int ix, int iy, int iz, int looked) {
     const DevWorld &w = P.w;
@@ -211,17 +209,26 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
             }
             if (in && VT_IN((unsigned)(qx >> 3) < (unsigned)w.nbx && (unsigned)(qy >> 3) < (unsigned)w.nby && (unsigned)(qz >> 3) < (unsigned)w.nbz, 4)) {
                 const uint32_t b = __ldg(&w.brick_tab[((qx >> 3) * w.nby + (qy >> 3)) * w.nbz + (qz >> 3)]);
-                if (b && VT_IN(b <= w.pool_slots, 5)) mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
-                else if (L.res == 1 && P.brick_runs) {
-                    for (;;) {
+                // Brick-local loop (full-resolution chunks): every further sample that stays in this 8^3 brick -- same
+                // chunk (bricks never straddle chunks when chunk_size % 8 == 0), same table entry -- costs the position
+                // update, three floors and, in a non-empty brick, one byte load, instead of a whole trip through the
+                // state machine; the sample positions themselves are the reference's, one fp64 add per axis per sample.
+                // The world origin is a multiple of 8 here, so brick membership is tested on absolute cells.
+                if (L.res == 1 && P.brick_runs && VT_IN(b <= w.pool_slots, 5)) {
+                    const uint8_t *pb = w.pool + (size_t)(b ? b - 1u : 0u) * 512u;
+                    const int ax = ix + w.ox, ay = iy + w.oy, az = iz + w.oz;
+                    if (b) mat = __ldg(pb + (((ix & 7) << 6) | ((iy & 7) << 3) | (iz & 7)));
+                    while (!mat) {
                         L.step += 1.0;
                         L.px += L.vx; L.py += L.vy; L.pz += L.vz;       // vel * 1.0 == vel
                         if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
-                        const int jx = floor_i(L.px) - w.ox, jy = floor_i(L.py) - w.oy, jz = floor_i(L.pz) - w.oz;
-                        if ((((jx ^ ix) | (jy ^ iy) | (jz ^ iz)) & ~7) != 0) return;      // next sample: another brick
+                        const int jx = floor_i(L.px), jy = floor_i(L.py), jz = floor_i(L.pz);
+                        if ((((jx ^ ax) | (jy ^ ay) | (jz ^ az)) & ~7) != 0) return;      // next sample: another brick
                         if (COUNT) c.in_chunk++;
+                        if (b) mat = __ldg(pb + (((jx & 7) << 6) | ((jy & 7) << 3) | (jz & 7)));
                     }
-                }
+                } else if (b && VT_IN(b <= w.pool_slots, 5))
+                    mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
             }
         }
         if (mat) { L.st = (L.st & ~0xfffu) | ST_HIT | ((uint32_t)mat << 2); return; }
