@@ -295,6 +295,7 @@ struct vt_ctx {
     // persistent kernel state: per-pixel accumulators (zero between launches), ray queue, launch geometry
     unsigned long long *d_acc = nullptr; long long acc_cap = 0;     // in u64 words
     unsigned long long *d_queue = nullptr;
+    unsigned long long *d_pow_tab = nullptr; double pow_tab_falloff = 0.0; bool pow_tab_on = true;   // VT_POWTAB=0 disables
     int persist_blocks[8] = {0, 0, 0, 0, 0, 0, 0, 0};                          // resident blocks per SM, per instantiation
     int sm_count = 0;
     int max_res = 0;                                                // largest Frame.resolution in the chunk table
@@ -358,6 +359,13 @@ extern "C" int vt_create(int device, vt_ctx **out) {
     }
     if (const char *k = getenv("VT_KERNEL")) ctx->kernel_version = atoi(k) == 1 ? 1 : 2;
     if (const char *k = getenv("VT_RUNS")) ctx->brick_runs = atoi(k) != 0;
+    if (const char *k = getenv("VT_POWTAB")) ctx->pow_tab_on = atoi(k) != 0;
+    if ((e = cudaMalloc(&ctx->d_pow_tab, VT_POW_SLOTS * 2 * sizeof(unsigned long long))) != cudaSuccess ||
+        (e = cudaMemset(ctx->d_pow_tab, 0, VT_POW_SLOTS * 2 * sizeof(unsigned long long))) != cudaSuccess) {
+        g_create_err = std::string("vt_create: ") + cudaGetErrorString(e);
+        delete ctx;
+        return 2;
+    }
     if (const char *k = getenv("VT_REFILL")) { int v = atoi(k); if (v >= 1 && v <= 32) ctx->refill_min = v; }
     *out = ctx;
     return 0;
@@ -376,7 +384,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_world(ctx);
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
-    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_wait_status);
+    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_pow_tab); cudaFree(ctx->d_wait_status);
     for (int k = 0; k < 4; k++) cudaFree(ctx->fx_buf[k]);
     for (int k = 0; k < VT_STAGES; k++) { if (ctx->stage[k].h) cudaFreeHost(ctx->stage[k].h); if (ctx->stage[k].ev) cudaEventDestroy(ctx->stage[k].ev); }
     cudaFree(ctx->d_fx_sums); cudaFree(ctx->d_fx_avg); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
@@ -922,6 +930,11 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
         ctx->acc_cap = words;
     }
     P.acc = ctx->d_acc; P.queue = ctx->d_queue; P.refill_min = ctx->refill_min;
+    if (ctx->pow_tab_falloff != s.falloff) {                 // the table holds pow(x, 1 + falloff) for one falloff
+        VT_CHECK(ctx, cudaMemsetAsync(ctx->d_pow_tab, 0, VT_POW_SLOTS * 2 * sizeof(unsigned long long), ctx->stream));
+        ctx->pow_tab_falloff = s.falloff;
+    }
+    P.pow_tab = ctx->pow_tab_on ? ctx->d_pow_tab : nullptr;
     P.brick_runs = (ctx->brick_runs && s.chunk_size % VT_BRICK == 0) ? 1 : 0;
     for (int r = 2; r <= VT_LOD_TAB; r++) {
         P.lod_magic[r] = (uint32_t)((1ull << 32) / (unsigned)r) + 1u;

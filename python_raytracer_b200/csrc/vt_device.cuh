@@ -14,7 +14,9 @@
 #include <cuda_runtime.h>
 #include "../../include/voxtrace.h"
 
-#define VT_LOD_TAB 16               // Frame.resolution values served by the multiply-high snap table
+#define VT_LOD_TAB 16
+#define VT_POW_BITS 16
+#define VT_POW_SLOTS (1 << VT_POW_BITS)               // Frame.resolution values served by the multiply-high snap table
 
 namespace vt {
 
@@ -73,6 +75,7 @@ struct DevParams {
     unsigned long long *queue;      // [0] next ray slot, [1] warps finished; both zero between launches
     unsigned int total_warps;       // warps launched
     int refill_min;                 // refill once this many lanes are idle
+    unsigned long long *pow_tab;    // [VT_POW_SLOTS][2] {bits of x, bits of pow(x, 1 + falloff)} filled as values occur; 0 = empty
     int brick_runs;                 // 1: chunk_size % 8 == 0, empty-brick runs allowed (VT_RUNS=0 disables, A/B)
     uint32_t lod_magic[VT_LOD_TAB + 1];   // floor(n / r) == umulhi(n, magic[r]) for n < 2^24 / r ... (r >= 2)
     int32_t lod_bias[VT_LOD_TAB + 1][3];  // world origin mod r per axis

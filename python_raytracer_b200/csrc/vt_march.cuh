@@ -57,6 +57,32 @@ __device__ __noinline__ double2 sincos_out(double a) {
 }
 __device__ __noinline__ double pow_out(double a, double b) { return pow(a, b); }
 
+// (1 + bounces) ^ (1 + falloff) of lib.material / material_background (lib.py:450, 465).  `bounces` is a sum of a few
+// material absorptions, so a frame asks for the same handful of values millions of times: they are kept in a small
+// table in device memory, filled by whoever computes a value first.  Entries only go from empty to {x, pow(x)} (key
+// by compare-and-swap, then the value; a reader that sees the key without the value computes it itself) and the
+// value stored is the one libdevice's pow returns for that x, so the table can never change a result.  The host
+// clears it when `falloff` changes.
+__device__ __noinline__ double pow_cached(unsigned long long *tab, double x, double y) {
+    const unsigned long long key = (unsigned long long)__double_as_longlong(x);
+    const uint32_t h = ((uint32_t)(key >> 32) ^ (uint32_t)key * 0x9E3779B1u) * 0x85EBCA6Bu;
+    unsigned long long *e = tab + 2 * (h >> (32 - VT_POW_BITS));
+    ulonglong2 kv = __ldcg(reinterpret_cast<const ulonglong2 *>(e));
+    if (kv.x != key && kv.x != 0ull) {                                  // taken by another value: second home
+        e = tab + 2 * ((h >> (32 - VT_POW_BITS)) ^ 1u);
+        kv = __ldcg(reinterpret_cast<const ulonglong2 *>(e));
+    }
+    if (kv.x == key && kv.y != 0ull) return __longlong_as_double((long long)kv.y);
+    const double v = pow(x, y);
+    const unsigned long long old = kv.x == key ? key : atomicCAS(e, 0ull, key);
+    if (old == 0ull || old == key) atomicExch(e + 1, (unsigned long long)__double_as_longlong(v));
+    return v;
+}
+__device__ __forceinline__ double bounce_pow(const DevParams &P, double bounces) {
+    if (bounces == 0.0) return 1.0;                                     // pow(1, y) == 1 exactly
+    return P.pow_tab ? pow_cached(P.pow_tab, 1.0 + bounces, 1.0 + P.s.falloff) : pow_out(1.0 + bounces, 1.0 + P.s.falloff);
+}
+
 // ---- Philox stream of one ray: key = global pixel index, counter = (block, sample, frame seed) --------------
 __device__ __forceinline__ double lane_rng_next(const DevParams &P, Lane &L) {
     uint32_t d = L.draw++;
@@ -263,7 +289,7 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
     double alb_r = __ldg(m + 0), alb_g = __ldg(m + 1), alb_b = __ldg(m + 2);
     double rough = __ldg(m + 3), absorb = __ldg(m + 4), emit = __ldg(m + 6);
     // pow(1, y) == 1 exactly: the first interaction of a ray (bounces == 0) needs no pow
-    double pw = (L.bounces == 0.0) ? 1.0 : pow_out(1.0 + L.bounces, 1.0 + s.falloff);
+    double pw = bounce_pow(P, L.bounces);
     double a = fmin(1.0, absorb / pw);
     double b2 = 1.0 - a;
     int cr = rint_i(i2d(L.col & 255) * b2 + alb_r * a);
@@ -337,7 +363,7 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
     const vt_settings &s = P.s;
     double cr = i2d(L.col & 255), cg = i2d((L.col >> 8) & 255), cb = i2d((L.col >> 16) & 255);
     if (s.background) {                                                      // lib.material_background, lib.py:463-476
-        double pw = (L.bounces == 0.0) ? 1.0 : pow_out(1.0 + L.bounces, 1.0 + s.falloff);
+        double pw = bounce_pow(P, L.bounces);
         double a = fmin(1.0, 1.0 / pw);
         double up = fmax(0.0, L.vy);
         double b2 = 1.0 - a;

@@ -20,7 +20,7 @@ from python_raytracer_b200 import GpuCamera, Settings, abi
 def run_variant(spec, frames=8, settings=None, workload=None):
     env = dict(kv.split("=", 1) for kv in spec.split(",") if kv)
     lib = env.pop("LIB", None)
-    for k in ("VT_KERNEL", "VT_REFILL", "VT_RUNS", "VT_POLICY", "VT_SHADE"):
+    for k in [k for k in os.environ if k.startswith("VT_")]:
         os.environ.pop(k, None)
     os.environ.update(env)
     if lib:
