@@ -99,6 +99,27 @@ __device__ __forceinline__ double lane_rng_rand(const DevParams &P, Lane &L, dou
     return (-1.0 + lane_rng_next(P, L) * 2.0) * amp;
 }
 
+// Three consecutive rand(amp) draws (the velocity jitter of lib.material, lib.py:458): same stream positions as three
+// lane_rng_rand calls, but the Philox blocks are fetched where all lanes need one together -- block (draw + 1) >> 1
+// serves both parities -- so a warp whose lanes sit at odd and even draw counts runs Philox twice, not three times.
+__device__ __forceinline__ void lane_rng_rand3(const DevParams &P, Lane &L, double amp, double &r0, double &r1, double &r2) {
+    r0 = r1 = r2 = 0.0;
+    if (amp == 0.0) return;                                                 // rand(0) draws nothing (lib.py:431-434)
+    const uint32_t d = L.draw;
+    const uint32_t pix = (L.xy >> 16) * (uint32_t)P.s.width + (L.xy & 0xffffu);
+    const uint4 a = philox_block((d + 1u) >> 1, lane_sample(L), P.seed_lo, P.seed_hi, pix);
+    double u0, u1, u2;
+    if (d & 1u) { u0 = u53m(L.w2, L.w3); u1 = u53m(a.x, a.y); u2 = u53m(a.z, a.w); }
+    else {
+        u0 = u53m(a.x, a.y); u1 = u53m(a.z, a.w);
+        const uint4 b = philox_block((d >> 1) + 1u, lane_sample(L), P.seed_lo, P.seed_hi, pix);
+        u2 = u53m(b.x, b.y);
+        L.w2 = b.z; L.w3 = b.w;
+    }
+    L.draw = d + 3u;
+    r0 = (-1.0 + u0 * 2.0) * amp; r1 = (-1.0 + u1 * 2.0) * amp; r2 = (-1.0 + u2 * 2.0) * amp;
+}
+
 // Integer divisions by run-time divisors (chunk sizes that are not powers of two, resolutions above the snap table)
 // live in functions that are never inlined: inlined, ptxas if-converts the rare branch and every sample pays for a
 // 20-instruction division it does not use.
@@ -298,7 +319,8 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
     L.col = cr | (cg << 8) | (cb << 16);
     L.energy = L.energy * b2 + emit * a;
     L.life *= 1.0 - (rough * a);
-    double jx = lane_rng_rand(P, L, rough), jy = lane_rng_rand(P, L, rough), jz = lane_rng_rand(P, L, rough);
+    double jx, jy, jz;
+    lane_rng_rand3(P, L, rough, jx, jy, jz);
     L.vx += jx; L.vy += jy; L.vz += jz;
     // ---- init.py:82-86 ----
     L.bounces += absorb;
