@@ -285,7 +285,28 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
             if (!(L.step < L.life)) lane_set_state(L, ST_DONE);
             return;
         }
+#if VT_LODLOOP
+        // LOD chunk: keep stepping by `resolution` while the samples stay strictly inside this chunk's box
+        {
+            const unsigned cs = (unsigned)P.s.chunk_size;
+            const double dr = i2d(L.res);
+            for (;;) {
+                L.step += dr;
+                L.px += L.vx * dr; L.py += L.vy * dr; L.pz += L.vz * dr;
+                if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
+                const int jx = floor_i(L.px) - w.ox, jy = floor_i(L.py) - w.oy, jz = floor_i(L.pz) - w.oz;
+                if (max((unsigned)(jx - L.cx), max((unsigned)(jy - L.cy), (unsigned)(jz - L.cz))) >= cs) return;
+                if (COUNT) c.in_chunk++;
+                const int qx = lod_snap<FAST>(P, L.res, jx, 0), qy = lod_snap<FAST>(P, L.res, jy, 1), qz = lod_snap<FAST>(P, L.res, jz, 2);
+                if (qx >= L.cx && qy >= L.cy && qz >= L.cz) {
+                    const int m2 = cell_at(w, qx, qy, qz);
+                    if (m2) { L.st = (L.st & ~0xfffu) | ST_HIT | ((uint32_t)m2 << 2); return; }
+                }
+            }
+        }
+#else
         advance(L, i2d(L.res));
+#endif
     } else {
         if (COUNT) c.in_void++;
         advance(L, void_step2<FAST>(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift));
@@ -525,6 +546,9 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
 #endif
 #ifndef VT_TRIPS           // dev instrumentation (tools/kbench.py KB_COUNTERS): phase trip counts in counters[8..13]
 #define VT_TRIPS 0
+#endif
+#ifndef VT_LODLOOP
+#define VT_LODLOOP 1
 #endif
 #ifndef VT_MINB
 #define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
