@@ -132,3 +132,21 @@ def test_empty_and_ragged_regions():
     band = cam.render(rect=(1, 0, 63, 48), stripes=(5, 3, 1), want=("rgba8",))["rgba8"].cpu().numpy()
     assert np.array_equal(band, full[rows][:, 1:63])
     cam.close()
+
+
+def test_psnr_256spp_against_the_references_generator():
+    """256 spp on a crop grid (the wide two-word accumulator path, > 64 samples).  The GPU frame (Philox)
+    equals the oracle's Philox frame exactly and differs from the frame drawn with the reference's own generator
+    (MT19937 re-seeded per sample) by sampling noise only."""
+    from oracle import cport
+    from tests.test_oracle_golden import _crop_pixels, _psnr
+    c = dict(load_case("c3_cubes"))
+    c["pixels"] = _crop_pixels(c)
+    g = gpu_case(c, want=("mean",), samples=256)
+    sd = dict(c["settings"]); sd["samples"] = 256
+    world = cport.World(c["origin"], c["cells"], c["chunk_res"], c["materials"])
+    args = (sd, c["cam_pos"], c["cam_rot"], float(c["cam_lens"]), world)
+    ph = cport.render(*args, pixels=c["pixels"], rng=cport.RNG_PHILOX, seed=0)["mean"]
+    mt = cport.render(*args, pixels=c["pixels"], rng=cport.RNG_MT19937)["mean"]
+    assert np.abs(g["mean"].astype(np.float64) - ph).max() <= 255.0 * 2.0 ** -23       # f32 store of the f64 mean
+    assert _psnr(g["mean"].astype(np.float64), mt) >= 46.0
