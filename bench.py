@@ -259,7 +259,7 @@ def run_ours(args, rank, world, local_rank):
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (render_kernel): algorithmic bytes from its own counters -----------
+    # ---- roofline of the dominant kernel (render_persistent): algorithmic bytes from its own counters -----------
     alg_bytes, cnt_tot = 0.0, np.zeros(8, dtype=np.int64)
     for i in range(args.steps):
         set_pose(args.warmup + i)

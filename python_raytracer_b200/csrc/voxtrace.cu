@@ -16,86 +16,6 @@ using namespace vt;
 // ------------------------------------------------------------------------------------------------------
 // kernels
 
-// Camera.tile (reference init.py:126-150).  One warp renders one small pixel tile; each pixel owns G adjacent lanes
-// (G = samples rounded up to a power of two, at most 32) so the samples of a pixel -- near-identical rays -- march
-// in lock step, and the per-pixel mean (lib.average, lib.py:419-428) is a shuffle reduction.  All sums are sums of
-// integers held in doubles, so the order of additions cannot change the result.
-template <bool REC, bool FULL_TAIL>
-__global__ void __launch_bounds__(128) render_kernel(const __grid_constant__ DevParams P, const int32_t *__restrict__ row_y) {
-    const vt_settings &s = P.s;
-    const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const long long warp = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    if (warp >= P.n_warps) return;                                       // uniform per warp
-    const int G = P.group, sl = lane & (G - 1), pi = lane >> P.group_shift;
-    bool pv; int x = 0, y = 0; long long i = 0;
-    if (P.pixels) {
-        i = warp * (32 >> P.group_shift) + pi;
-        pv = i < P.n_pixels;
-        if (pv) { x = __ldg(P.pixels + 2 * i); y = __ldg(P.pixels + 2 * i + 1); }
-    } else {
-        const int bw = P.x1 - P.x0;
-        long long ty = warp / P.tiles_x; int tx = (int)(warp - ty * P.tiles_x);
-        int lx = pi & (P.tile_w - 1), ly = pi >> P.tile_w_shift;
-        int col = tx * P.tile_w + lx; long long lr = ty * P.tile_h + ly;
-        pv = col < bw && lr < P.band_rows;
-        if (pv) { x = P.x0 + col; y = __ldg(row_y + lr); i = lr * bw + col; }
-    }
-    double dir_x = -1.0 + ((double)x / (double)s.width) * 2.0;           // init.py:131-134
-    double dir_y = -1.0 + ((double)y / (double)s.height) * 2.0;
-    double detail = 1.0 - fabs(dir_x * dir_y) * s.lod_edge;
-    int n = (int)rint((double)s.samples * detail);
-    if (n < 1) n = 1;
-    if (!pv) n = 0;
-    const unsigned long long pix = (unsigned long long)y * (unsigned long long)s.width + (unsigned long long)x;
-    Counters c = {0, 0, 0, 0, 0, 0};
-    unsigned rays = 0;
-    double sum_r = 0.0, sum_g = 0.0, sum_b = 0.0, sum_a = 0.0;
-    for (int sample = sl; __any_sync(full, sample < n); sample += G) {
-        const bool valid = sample < n;
-        Rng g;
-        g.key0 = (uint32_t)pix; g.key1 = (uint32_t)(pix >> 32);
-        g.sample = (uint32_t)sample; g.seed_lo = P.seed_lo; g.seed_hi = P.seed_hi; g.draw = 0; g.w2 = g.w3 = 0;
-        double u = rng_next(g);                                           // drawn even when lod_random == 0 (init.py:139)
-        double ray_detail = detail / (1.0 + (double)sample * s.lod_samples) * (1.0 - s.lod_random * u);
-        Ray r;
-        trace_warp<FULL_TAIL>(P, valid, dir_x, dir_y, ray_detail, g, r, c, x, y);
-        if (valid) {
-            rays++;
-            double alpha = rint(fmin(1.0, r.energy + s.shutter) * 255.0); // init.py:141
-            sum_r += r.cr; sum_g += r.cg; sum_b += r.cb; sum_a += alpha;
-            if (REC && sample == 0) {
-                double *o = P.ray0 + (size_t)VT_RAY_RECORD * i;
-                o[0] = r.cr; o[1] = r.cg; o[2] = r.cb; o[3] = r.energy; o[4] = r.bounces; o[5] = r.step;
-                o[6] = (double)r.hits; o[7] = (double)r.fx; o[8] = (double)r.fy; o[9] = (double)r.fz;
-                o[10] = (double)r.fflag; o[11] = r.first_step; o[12] = r.vx; o[13] = r.vy; o[14] = r.vz; o[15] = (double)n;
-            }
-        }
-    }
-    for (int off = G >> 1; off; off >>= 1) {
-        sum_r += __shfl_xor_sync(full, sum_r, off); sum_g += __shfl_xor_sync(full, sum_g, off);
-        sum_b += __shfl_xor_sync(full, sum_b, off); sum_a += __shfl_xor_sync(full, sum_a, off);
-    }
-    if (pv && sl == 0) {
-        double dn = (double)n;
-        double mr = sum_r / dn, mg = sum_g / dn, mb = sum_b / dn, ma = sum_a / dn;
-        if (P.mean) reinterpret_cast<float4 *>(P.mean)[i] = make_float4((float)mr, (float)mg, (float)mb, (float)ma);
-        if (P.rgba8) {
-            uchar4 q;                                                     // truncation, like a C cast
-            q.x = (unsigned char)fmin(255.0, mr); q.y = (unsigned char)fmin(255.0, mg);
-            q.z = (unsigned char)fmin(255.0, mb); q.w = (unsigned char)fmin(255.0, ma);
-            reinterpret_cast<uchar4 *>(P.rgba8)[i] = q;
-        }
-    }
-    if (P.counters) {
-        unsigned v[7] = {rays, c.in_chunk, c.in_void, c.hits, c.probes, c.rechunk, c.iters};
-#pragma unroll
-        for (int k = 0; k < 7; k++) {
-            unsigned t = __reduce_add_sync(full, v[k]);
-            if (lane == 0 && t) atomicAdd(P.counters + k, (unsigned long long)t);
-        }
-    }
-}
 
 // scatter m staged bricks into their pool slots and patch the brick table
 __global__ void scatter_bricks_kernel(const uint8_t *__restrict__ staged, const uint32_t *__restrict__ slots,
@@ -299,7 +219,6 @@ struct vt_ctx {
     int persist_blocks[8] = {0, 0, 0, 0, 0, 0, 0, 0};                          // resident blocks per SM, per instantiation
     int sm_count = 0;
     int max_res = 0;                                                // largest Frame.resolution in the chunk table
-    int kernel_version = 2;                                         // VT_KERNEL=1 selects the v1 warp-tile kernel (A/B)
     int brick_runs = 1;                                             // VT_RUNS=0 disables empty-brick runs (A/B)
     int refill_min = 32;                                            // VT_REFILL overrides
     // multi-GPU frame target (vt_set_frame_target) and the status word of the wait kernel
@@ -357,7 +276,6 @@ extern "C" int vt_create(int device, vt_ctx **out) {
         delete ctx;
         return 2;
     }
-    if (const char *k = getenv("VT_KERNEL")) ctx->kernel_version = atoi(k) == 1 ? 1 : 2;
     if (const char *k = getenv("VT_RUNS")) ctx->brick_runs = atoi(k) != 0;
     if (const char *k = getenv("VT_POWTAB")) ctx->pow_tab_on = atoi(k) != 0;
     if ((e = cudaMalloc(&ctx->d_pow_tab, VT_POW_SLOTS * 2 * sizeof(unsigned long long))) != cudaSuccess ||
@@ -1018,8 +936,8 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
     }
     if (P.n_pixels == 0) return 0;
     P.frame_target = ctx->frame_target; P.arrive_flag = ctx->arrive_flag; P.arrive_value = ctx->arrive_value;
-    if (ctx->frame_target && (ctx->kernel_version == 1 || region->dev_pixels))
-        return fail(ctx, "vt_render: a frame target needs the persistent kernel and a rectangle region");
+    if (ctx->frame_target && region->dev_pixels)
+        return fail(ctx, "vt_render: a frame target needs a rectangle region");
     P.rgba8 = dev_rgba8; P.mean = dev_mean; P.ray0 = dev_ray0; P.visited = dev_visited;
     P.counters = reinterpret_cast<unsigned long long *>(dev_counters);
     // lanes per pixel: samples rounded up to a power of two (<= 32); pixels per warp form a small 2-D tile
@@ -1035,16 +953,7 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
         P.tiles_x = (P.x1 - P.x0 + tw - 1) / tw;
         P.n_warps = (long long)P.tiles_x * ((P.band_rows + P.tile_h - 1) / P.tile_h);
     }
-    const int block = 128;
-    if (ctx->kernel_version == 1) {
-        long long blocks = (P.n_warps + (block / 32) - 1) / (block / 32);
-        if (blocks > 0x7fffffffLL) return fail(ctx, "vt_render: region too large for one launch");
-        int grid = (int)blocks;
-        if (dev_ray0) render_kernel<true, true><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
-        else render_kernel<false, false><<<grid, block, 0, ctx->stream>>>(P, ctx->d_row_y);
-    } else {
-        if (int rc = launch_persistent(ctx, P, dev_ray0 != nullptr, dev_counters != nullptr)) return rc;
-    }
+    if (int rc = launch_persistent(ctx, P, dev_ray0 != nullptr, dev_counters != nullptr)) return rc;
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     return 0;

@@ -1,7 +1,6 @@
-// vt_march.cuh — persistent ray-march kernel (render kernel v2) for sm_100a.
-//
-// Same arithmetic as vt_device.cuh's trace_warp (reference init.py:37-150, lib.py:448-476, data.py:136-145) --
-// every ray produces the same sample positions, hits and colours -- but scheduled differently:
+// vt_march.cuh — persistent ray-march kernel for sm_100a: Camera.tile / Camera.trace (reference init.py:37-150),
+// lib.material / material_background (lib.py:448-476) and Frame.get_voxel (data.py:136-145) for a whole frame.
+// Every ray produces the reference's sample positions, hits and colours; what is specific to the GPU is the schedule:
 //
 //   * One persistent grid per frame.  Every LANE owns one ray at a time and fetches the next ray slot from a
 //     global queue when its ray ends (rays of a frame differ in length by 10x, so a warp that waits for its

@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Kernel A/B timing on the bench workload (dev tool, not a test):  python tools/kbench.py [variant ...]
 
-A variant is a comma-separated list of ENV=VALUE pairs read by vt_create (VT_KERNEL=1|2, VT_REFILL=n) plus
+A variant is a comma-separated list of ENV=VALUE pairs read by vt_create (VT_REFILL=n, VT_RUNS=0, VT_POWTAB=0) plus
 optionally LIB=<path to an alternative libvoxtrace.so>.  Prints ms/frame per camera pose.
 """
 import json
@@ -69,5 +69,5 @@ def run_variant(spec, frames=8, settings=None, workload=None):
 
 
 if __name__ == "__main__":
-    for spec in (sys.argv[1:] or ["VT_KERNEL=1", "VT_KERNEL=2"]):
+    for spec in (sys.argv[1:] or [""]):
         run_variant(spec)
