@@ -95,7 +95,9 @@ class FrameRenderer(StripeGather):
     def submit_frame(self, pos, rot, chunk_res, host_rgba8):
         """Like frame_to_host but returns at once with a ticket; ``wait(ticket)`` blocks until ``host_rgba8`` holds
         the frame.  Two device frames alternate, the copy runs on its own stream."""
-        assert self.world == 1, "the pipelined multi-GPU path is PeerFrameRenderer.submit_frame"
+        if self.world > 1:              # the NCCL gather baseline stays blocking; PeerFrameRenderer is the pipelined path
+            self.frame_to_host(pos, rot, chunk_res, host_rgba8)
+            return None
         dev = self.cam.device
         if not hasattr(self, "_pipe"):
             self._pipe = dict(frames=[torch.zeros_like(self.frame) for _ in range(2)], copy=torch.cuda.Stream(dev),
