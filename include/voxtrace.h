@@ -83,8 +83,15 @@ int vt_set_chunk_table(vt_ctx *ctx, const uint8_t *host_res, int64_t n_slots);
  * its storage.  Stands in for chunk_set replacing one chunk's Frame (init.py:21-25, 450-452). */
 int vt_upload_bricks(vt_ctx *ctx, const int32_t *host_brick_coords, const uint8_t *host_cells, int m);
 /* Bulk path for synthetic / imported worlds: a dense [dims0][dims1][dims2] (z fastest) u8 array in DEVICE
- * memory is bricked on the device; empty bricks get no storage. */
+ * memory is bricked on the device; empty bricks get no storage.  Three streaming launches (occupancy bits, slot
+ * scan, pack); pool slots follow brick-index order; the only host step is reading the brick count (8 bytes). */
 int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells);
+/* The inverse: the world held in bricks written out as a dense [dims0][dims1][dims2] u8 array in DEVICE memory. */
+int vt_download_dense(vt_ctx *ctx, uint8_t *dev_cells);
+/* Which chunk slots hold a voxel -- what `post_chunk in self.chunks` answers once chunk_update has run
+ * (init.py:441-452), before LOD and culling: [dims0/cs][dims1/cs][dims2/cs] bytes (z fastest, 0 / 1) into HOST
+ * memory, derived from the brick table on the device.  chunk_size must be a multiple of 8. */
+int vt_chunk_presence(vt_ctx *ctx, uint8_t *host_present, int64_t n_slots);
 /* Bytes of device memory held by bricks / number of non-empty bricks (reporting). */
 int vt_world_stats(vt_ctx *ctx, int64_t *n_bricks, int64_t *bytes);
 

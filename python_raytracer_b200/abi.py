@@ -13,7 +13,7 @@ RAY_RECORD = 16
 
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
            "vt_set_settings", "vt_set_materials", "vt_set_camera", "vt_set_world", "vt_set_chunk_table",
-           "vt_upload_bricks", "vt_upload_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
+           "vt_upload_bricks", "vt_upload_dense", "vt_chunk_presence", "vt_download_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
            "vt_launch_count", "vt_build_flags", "vt_build_world", "vt_update_region", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
            "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
@@ -81,6 +81,8 @@ def load(path: str | None = None):
         "vt_set_chunk_table": (C.c_int, [vp, vp, i64]),
         "vt_upload_bricks": (C.c_int, [vp, vp, vp, i32]),
         "vt_upload_dense": (C.c_int, [vp, vp]),
+        "vt_chunk_presence": (C.c_int, [vp, vp, i64]),
+        "vt_download_dense": (C.c_int, [vp, vp]),
         "vt_world_stats": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
         "vt_render": (C.c_int, [vp, C.POINTER(VtRegion), vp, vp, vp, vp, vp, u64]),
         "vt_region_pixels": (i64, [C.POINTER(VtRegion)]),

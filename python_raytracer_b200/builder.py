@@ -122,15 +122,18 @@ class WorldBuilder:
         torch.cuda.synchronize(cam.device)
         cam._check(lib.vt_build_world(ctx, arr, len(objects), cells.data_ptr()))
         cam._check(lib.vt_upload_dense(ctx, cells.data_ptr()))
-        ncx, ncy, ncz = (int(v) // cs for v in dims)
-        self.present = cells.view(ncx, cs, ncy, cs, ncz, cs).amax(dim=(1, 3, 5)).ne(0).cpu().numpy()
+        cam._world_origin = origin
+        cam._world_shape = tuple(int(v) for v in dims)
+        if cs % 8 == 0:
+            self.present = cam.chunk_presence()                # from the brick table, on the device
+        else:
+            ncx, ncy, ncz = (int(v) // cs for v in dims)
+            self.present = cells.view(ncx, cs, ncy, cs, ncz, cs).amax(dim=(1, 3, 5)).ne(0).cpu().numpy()
         self.cells, self.origin = cells, origin
         self.order = list(objects)
         self.drawn = {id(o): chunk_box(o, cs) for o in objects}
         cam._dense_mode = True
         cam.chunks = {}
-        cam._world_origin = origin
-        cam._world_shape = tuple(int(v) for v in dims)
         cam._static_materials = np.ascontiguousarray(materials, dtype=np.float64)
         self.update_lod(visible=None)
         return cells

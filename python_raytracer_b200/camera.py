@@ -79,6 +79,8 @@ class GpuCamera:
         self._counters = torch.zeros(16, dtype=torch.int64, device=self.device)
         self._pix_cache = {}
         self._static_materials = None
+        self._world_shape = None
+        self._world_origin = None
 
     # ------------------------------------------------------------------ plumbing
     def _check(self, rc):
@@ -249,6 +251,32 @@ class GpuCamera:
         self._check(self._lib.vt_set_chunk_table(self._ctx, t.ctypes.data, t.size))
         self._chunk_res_shape = t.shape
         self._visited = None
+
+    def download_dense(self):
+        """The world held in bricks as a dense [nx, ny, nz] u8 CUDA tensor (inverse of ``set_world_dense``)."""
+        if self._dense_mode:
+            shape = self._world_shape
+        else:
+            self._sync_world()
+            shape = tuple(int(v) for v in self._mirror.cells.shape)
+        if shape is None:
+            raise VoxtraceError("download_dense: no world")
+        out = torch.empty(shape, dtype=torch.uint8, device=self.device)
+        torch.cuda.synchronize(self.device)
+        self._check(self._lib.vt_download_dense(self._ctx, out.data_ptr()))
+        return out
+
+    def chunk_presence(self):
+        """[ncx, ncy, ncz] bool: chunk slots that hold a voxel (``post_chunk in self.chunks`` after chunk_update,
+        init.py:441-452), derived on the device from the brick table.  chunk_size % 8 == 0 only."""
+        cs = int(self.settings.chunk_size)
+        if not self._dense_mode:
+            self._sync_world()
+        world = self._world_shape if self._dense_mode else tuple(int(v) for v in self._mirror.cells.shape)
+        shape = tuple(v // cs for v in world)
+        out = np.empty(shape, np.uint8)
+        self._check(self._lib.vt_chunk_presence(self._ctx, out.ctypes.data, out.size))
+        return out.astype(bool)
 
     def world_stats(self):
         nb, by = C.c_int64(), C.c_int64()

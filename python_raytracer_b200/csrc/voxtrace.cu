@@ -10,154 +10,13 @@
 
 #include "vt_device.cuh"
 #include "vt_march.cuh"
+#include "vt_scene.cuh"
 
 using namespace vt;
 
 // ------------------------------------------------------------------------------------------------------
 // kernels
 
-
-// scatter m staged bricks into their pool slots and patch the brick table
-__global__ void scatter_bricks_kernel(const uint8_t *__restrict__ staged, const uint32_t *__restrict__ slots,
-                                      const uint32_t *__restrict__ tab_index, const uint32_t *__restrict__ tab_value,
-                                      uint8_t *pool, uint32_t *brick_tab, int m) {
-    int b = blockIdx.x;
-    if (b >= m) return;
-    uint32_t slot = slots[b];
-    if (slot != 0xffffffffu) {
-        const uint4 *src = reinterpret_cast<const uint4 *>(staged + (size_t)b * 512);
-        uint4 *dst = reinterpret_cast<uint4 *>(pool + (size_t)slot * 512);
-        dst[threadIdx.x] = src[threadIdx.x];          // 32 threads x 16 B
-    }
-    if (threadIdx.x == 0) brick_tab[tab_index[b]] = tab_value[b];
-}
-
-// dense [nx][ny][nz] -> per-brick "has any solid cell" flag
-__global__ void brick_flags_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nbx, int nby, int nbz,
-                                   uint8_t *flags) {
-    long long nb = (long long)nbx * nby * nbz;
-    for (long long b = (long long)blockIdx.x * blockDim.x + threadIdx.x; b < nb; b += (long long)gridDim.x * blockDim.x) {
-        int bz = (int)(b % nbz), by = (int)((b / nbz) % nby), bx = (int)(b / ((long long)nbz * nby));
-        unsigned any = 0;
-        for (int lx = 0; lx < 8 && !any; lx++)
-            for (int ly = 0; ly < 8 && !any; ly++) {
-                int x = bx * 8 + lx, y = by * 8 + ly;
-                if (x >= nx || y >= ny) continue;
-                for (int lz = 0; lz < 8; lz++) {
-                    int z = bz * 8 + lz;
-                    if (z < nz && dense[((size_t)x * ny + y) * nz + z]) { any = 1; break; }
-                }
-            }
-        flags[b] = (uint8_t)any;
-    }
-}
-
-// copy dense cells of every non-empty brick into its pool slot (one block of 512 threads per brick)
-__global__ void brick_fill_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nby, int nbz,
-                                  const uint32_t *__restrict__ brick_tab, long long nb, uint8_t *pool) {
-    for (long long b = blockIdx.x; b < nb; b += gridDim.x) {
-        uint32_t slot1 = brick_tab[b];
-        if (!slot1) continue;
-        int bz = (int)(b % nbz), by = (int)((b / nbz) % nby), bx = (int)(b / ((long long)nbz * nby));
-        int t = threadIdx.x, lx = t >> 6, ly = (t >> 3) & 7, lz = t & 7;
-        int x = bx * 8 + lx, y = by * 8 + ly, z = bz * 8 + lz;
-        uint8_t v = (x < nx && y < ny && z < nz) ? dense[((size_t)x * ny + y) * nz + z] : 0;
-        pool[(size_t)(slot1 - 1) * 512 + t] = v;
-    }
-}
-
-// Sprite.pos_rotated (reference data.py:338-371): 90-degree steps, each axis only when the two other sizes match
-__device__ __forceinline__ void pos_rotated(const vt_object &o, int &x, int &y, int &z) {
-    const int ex = o.size[0] - 1, ey = o.size[1] - 1, ez = o.size[2] - 1;
-    int ax = o.angle[0], ay = o.angle[1], az = o.angle[2], nx, ny, nz;
-    if (ax && o.size[1] == o.size[2]) {
-        if (ax == 1) { ny = ez - z; nz = y; } else if (ax == 2) { ny = ey - y; nz = ez - z; } else { ny = z; nz = ey - y; }
-        y = ny; z = nz;
-    }
-    if (ay && o.size[0] == o.size[2]) {
-        if (ay == 1) { nx = z; nz = ex - x; } else if (ay == 2) { nx = ex - x; nz = ez - z; } else { nx = ez - z; nz = x; }
-        x = nx; z = nz;
-    }
-    if (az && o.size[0] == o.size[1]) {
-        if (az == 1) { nx = ey - y; ny = x; } else if (az == 2) { nx = ex - x; ny = ey - y; } else { nx = y; ny = ex - x; }
-        x = nx; y = ny;
-    }
-}
-
-// Window.chunk_update's voxel gathering (init.py:413-424, 437-439) as one pass over the world's cells: the last
-// object in list order that has a voxel at the cell wins.
-__global__ void build_world_kernel(const vt_object *__restrict__ objs, int n, int ox, int oy, int oz, int nx, int ny, int nz,
-                                   uint8_t *__restrict__ cells) {
-    const long long total = (long long)nx * ny * nz;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        int z = (int)(i % nz), y = (int)((i / nz) % ny), x = (int)(i / ((long long)nz * ny));
-        const int wx = x + ox, wy = y + oy, wz = z + oz;
-        uint8_t m = 0;
-        for (int k = n - 1; k >= 0 && !m; k--) {
-            const vt_object &o = objs[k];
-            if (wx < o.mins[0] || wx >= o.maxs[0] || wy < o.mins[1] || wy >= o.maxs[1] || wz < o.mins[2] || wz >= o.maxs[2]) continue;
-            int lx = wx - o.mins[0], ly = wy - o.mins[1], lz = wz - o.mins[2];
-            pos_rotated(o, lx, ly, lz);
-            if ((unsigned)lx >= (unsigned)o.size[0] || (unsigned)ly >= (unsigned)o.size[1] || (unsigned)lz >= (unsigned)o.size[2]) continue;
-            m = o.dev_sprite[((size_t)lx * o.size[1] + ly) * o.size[2] + lz];
-        }
-        cells[i] = m;
-    }
-}
-
-// Same for the cells of a box [lo, lo + ext) of the grid only (dirty chunks of objects that moved).
-__global__ void build_region_kernel(const vt_object *__restrict__ objs, int n, int ox, int oy, int oz, int ny, int nz,
-                                    int lx0, int ly0, int lz0, int ex, int ey, int ez, uint8_t *__restrict__ cells) {
-    const long long total = (long long)ex * ey * ez;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int x = lx0 + (int)(i / ((long long)ez * ey)), y = ly0 + (int)((i / ez) % ey), z = lz0 + (int)(i % ez);
-        const int wx = x + ox, wy = y + oy, wz = z + oz;
-        uint8_t m = 0;
-        for (int k = n - 1; k >= 0 && !m; k--) {
-            const vt_object &o = objs[k];
-            if (wx < o.mins[0] || wx >= o.maxs[0] || wy < o.mins[1] || wy >= o.maxs[1] || wz < o.mins[2] || wz >= o.maxs[2]) continue;
-            int lx = wx - o.mins[0], ly = wy - o.mins[1], lz = wz - o.mins[2];
-            pos_rotated(o, lx, ly, lz);
-            if ((unsigned)lx >= (unsigned)o.size[0] || (unsigned)ly >= (unsigned)o.size[1] || (unsigned)lz >= (unsigned)o.size[2]) continue;
-            m = o.dev_sprite[((size_t)lx * o.size[1] + ly) * o.size[2] + lz];
-        }
-        cells[((size_t)x * ny + y) * nz + z] = m;
-    }
-}
-
-// one warp per brick of the box of bricks [b0, b0 + nbr): flags[i] = brick holds a voxel
-__global__ void region_flags_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int bx0, int by0, int bz0,
-                                    int rbx, int rby, int rbz, uint8_t *flags) {
-    const int warps = (gridDim.x * blockDim.x) >> 5, lane = threadIdx.x & 31;
-    const int total = rbx * rby * rbz;
-    for (int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < total; i += warps) {
-        const int bz = bz0 + i % rbz, by = by0 + (i / rbz) % rby, bx = bx0 + i / (rbz * rby);
-        unsigned any = 0;
-        for (int t = lane; t < 512; t += 32) {
-            const int x = bx * 8 + (t >> 6), y = by * 8 + ((t >> 3) & 7), z = bz * 8 + (t & 7);
-            if (x < nx && y < ny && z < nz) any |= dense[((size_t)x * ny + y) * nz + z];
-        }
-        any = __any_sync(0xffffffffu, any != 0);
-        if (lane == 0) flags[i] = (uint8_t)any;
-    }
-}
-
-// copy the region's non-empty bricks from the dense grid into their pool slots and patch the brick table
-// (one block of 512 threads per brick; slot 0xffffffff = brick became empty)
-__global__ void region_fill_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nby, int nbz, int bx0, int by0,
-                                   int bz0, int rby, int rbz, const uint32_t *__restrict__ slots, int m, uint8_t *pool,
-                                   uint32_t *brick_tab) {
-    for (int i = blockIdx.x; i < m; i += gridDim.x) {
-        const int bz = bz0 + i % rbz, by = by0 + (i / rbz) % rby, bx = bx0 + i / (rbz * rby);
-        const uint32_t slot = slots[i];
-        const int t = threadIdx.x;
-        if (slot != 0xffffffffu) {
-            const int x = bx * 8 + (t >> 6), y = by * 8 + ((t >> 3) & 7), z = bz * 8 + (t & 7);
-            pool[(size_t)slot * 512 + t] = (x < nx && y < ny && z < nz) ? dense[((size_t)x * ny + y) * nz + z] : 0;
-        }
-        if (t == 0) brick_tab[((size_t)bx * nby + by) * nbz + bz] = slot == 0xffffffffu ? 0u : slot + 1u;
-    }
-}
 
 // Peer-memory handshakes of the multi-GPU frame path.  Flags are u32 words in cudaMalloc'ed memory
 // that peers reach through CUDA IPC; values only grow (frame sequence numbers), so a waiter never misses one.
@@ -207,6 +66,10 @@ struct vt_ctx {
     uint8_t *d_chunk_res = nullptr;
     uint32_t *d_brick_tab = nullptr;
     std::vector<uint32_t> h_brick_tab;          // host mirror: 0 = empty else slot + 1
+    bool mirror_stale = false;                  // vt_upload_dense numbered the slots on the device: mirror not fetched yet
+    // scene-building scratch (grow-only device buffers) and one pinned word for the device-side brick count
+    void *scene_buf[3] = {nullptr, nullptr, nullptr}; size_t scene_cap[3] = {0, 0, 0};
+    unsigned long long *h_word = nullptr;
     uint8_t *d_pool = nullptr;
     long long pool_cap = 0, pool_used = 0;      // in bricks
     std::vector<uint32_t> free_slots;
@@ -293,6 +156,7 @@ static void free_world(vt_ctx *ctx) {
     cudaFree(ctx->d_chunk_res); cudaFree(ctx->d_brick_tab); cudaFree(ctx->d_pool);
     ctx->d_chunk_res = nullptr; ctx->d_brick_tab = nullptr; ctx->d_pool = nullptr;
     ctx->pool_cap = ctx->pool_used = 0; ctx->free_slots.clear(); ctx->h_brick_tab.clear();
+    ctx->mirror_stale = false;
     ctx->have_world = false;
 }
 
@@ -304,6 +168,8 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
     cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_pow_tab); cudaFree(ctx->d_wait_status);
     for (int k = 0; k < 4; k++) cudaFree(ctx->fx_buf[k]);
+    for (int k = 0; k < 3; k++) cudaFree(ctx->scene_buf[k]);
+    if (ctx->h_word) cudaFreeHost(ctx->h_word);
     for (int k = 0; k < VT_STAGES; k++) { if (ctx->stage[k].h) cudaFreeHost(ctx->stage[k].h); if (ctx->stage[k].ev) cudaEventDestroy(ctx->stage[k].ev); }
     cudaFree(ctx->d_fx_sums); cudaFree(ctx->d_fx_avg); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -439,18 +305,72 @@ static int grow_pool(vt_ctx *ctx, long long need) {
     return 0;
 }
 
+// Grow-only device scratch of the scene-building calls (object list, task tables, flags): no cudaMalloc / cudaFree --
+// each of which synchronises the device -- on the per-update path.
+static int scene_scratch(vt_ctx *ctx, int which, size_t bytes, void **out) {
+    if (bytes == 0) bytes = 16;
+    if (ctx->scene_cap[which] < bytes) {
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->scene_buf[which]);
+        ctx->scene_buf[which] = nullptr; ctx->scene_cap[which] = 0;
+        size_t cap = 4096;
+        while (cap < bytes) cap *= 2;
+        VT_CHECK(ctx, cudaMalloc(&ctx->scene_buf[which], cap));
+        ctx->scene_cap[which] = cap;
+    }
+    *out = ctx->scene_buf[which];
+    return 0;
+}
+
+// The host mirror of the brick table serves the in-place updates (slot reuse, free list).  vt_upload_dense numbers the
+// slots on the device and leaves the mirror stale; the first in-place update after it fetches the table once.
+static int ensure_mirror(vt_ctx *ctx) {
+    if (!ctx->mirror_stale) return 0;
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->h_brick_tab.data(), ctx->d_brick_tab, ctx->h_brick_tab.size() * sizeof(uint32_t),
+                                  cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    ctx->mirror_stale = false;
+    return 0;
+}
+
+static int check_objects(vt_ctx *ctx, const vt_object *objs, int n, const char *who) {
+    for (int k = 0; k < n; k++) {
+        if (!objs[k].dev_sprite) { ctx->err = std::string(who) + ": object without a sprite grid"; return 1; }
+        for (int a = 0; a < 3; a++) {
+            if (objs[k].size[a] <= 0) { ctx->err = std::string(who) + ": sprite size must be positive"; return 1; }
+            if (objs[k].angle[a] < 0 || objs[k].angle[a] > 3) { ctx->err = std::string(who) + ": angle must be 0..3"; return 1; }
+        }
+    }
+    return 0;
+}
+
+// object list -> device (scratch 0), through the pinned staging ring
+static int stage_objects(vt_ctx *ctx, const vt_object *objs, int n, vt_object **d_objs) {
+    void *p = nullptr;
+    if (int rc = scene_scratch(ctx, 0, (size_t)n * sizeof(vt_object), &p)) return rc;
+    *d_objs = static_cast<vt_object *>(p);
+    if (n) return staged_upload(ctx, p, objs, (size_t)n * sizeof(vt_object));
+    return 0;
+}
+
+static bool dense_vec(const vt_ctx *ctx, const uint8_t *dev_cells) {
+    return ctx->dims[2] % 8 == 0 && (reinterpret_cast<uintptr_t>(dev_cells) & 7u) == 0;
+}
+
 extern "C" int vt_upload_bricks(vt_ctx *ctx, const int32_t *coords, const uint8_t *cells, int m) {
     if (!ctx || (m > 0 && (!coords || !cells))) return 1;
     if (!ctx->have_world) return fail(ctx, "vt_upload_bricks: no world (vt_set_world)");
     if (m <= 0) return 0;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (int rc = ensure_mirror(ctx)) return rc;
+    for (int b = 0; b < m; b++)
+        for (int a = 0; a < 3; a++)
+            if (coords[3 * b + a] < 0 || coords[3 * b + a] >= ctx->nb[a]) return fail(ctx, "vt_upload_bricks: brick coordinate outside the world");
     std::vector<uint32_t> meta((size_t)m * 3);       // slots | table index | table value
     uint32_t *slots = meta.data(), *tidx = slots + m, *tval = tidx + m;
     long long need = ctx->pool_used;
     for (int b = 0; b < m; b++) {
         const int32_t *c = coords + 3 * b;
-        for (int a = 0; a < 3; a++)
-            if (c[a] < 0 || c[a] >= ctx->nb[a]) return fail(ctx, "vt_upload_bricks: brick coordinate outside the world");
         uint32_t ti = (uint32_t)(((long long)c[0] * ctx->nb[1] + c[1]) * ctx->nb[2] + c[2]);
         bool empty = true;
         const uint64_t *q = reinterpret_cast<const uint64_t *>(cells + (size_t)b * 512);
@@ -473,76 +393,77 @@ extern "C" int vt_upload_bricks(vt_ctx *ctx, const int32_t *coords, const uint8_
     }
     if (int rc = grow_pool(ctx, need)) return rc;
     ctx->pool_used = need;
-    uint8_t *d_stage = nullptr; uint32_t *d_meta = nullptr;
-    VT_CHECK(ctx, cudaMalloc(&d_stage, (size_t)m * 512));
-    VT_CHECK(ctx, cudaMalloc(&d_meta, meta.size() * sizeof(uint32_t)));
+    void *d_stage = nullptr, *d_meta_v = nullptr;
+    if (int rc = scene_scratch(ctx, 1, (size_t)m * 512, &d_stage)) return rc;
+    if (int rc = scene_scratch(ctx, 2, meta.size() * sizeof(uint32_t), &d_meta_v)) return rc;
+    uint32_t *d_meta = static_cast<uint32_t *>(d_meta_v);
     VT_CHECK(ctx, cudaMemcpyAsync(d_stage, cells, (size_t)m * 512, cudaMemcpyHostToDevice, ctx->stream));
     VT_CHECK(ctx, cudaMemcpyAsync(d_meta, meta.data(), meta.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
-    scatter_bricks_kernel<<<m, 32, 0, ctx->stream>>>(d_stage, d_meta, d_meta + m, d_meta + 2 * m, ctx->d_pool, ctx->d_brick_tab, m);
+    scatter_bricks_kernel<<<m, 32, 0, ctx->stream>>>(static_cast<const uint8_t *>(d_stage), d_meta, d_meta + m, d_meta + 2 * m, ctx->d_pool,
+                                                     ctx->d_brick_tab, m);
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_stage); cudaFree(d_meta);
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));       // `cells` and `meta` are free on return
     return 0;
 }
 
+// Dense world -> brick pool + brick table, entirely on the device: occupancy bits (one pass over the cells), an
+// exclusive scan of the per-task counts (slots in brick-index order), then the pack pass (second read of the cells,
+// mostly from L2 for worlds below ~100 MiB; one 512-byte store per non-empty brick).  The only host step is reading
+// the brick COUNT back (8 bytes, pinned) to size the pool.
 extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
     if (!ctx || !dev_cells) return 1;
     if (!ctx->have_world) return fail(ctx, "vt_upload_dense: no world (vt_set_world)");
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    const long long nb = (long long)ctx->nb[0] * ctx->nb[1] * ctx->nb[2];
-    uint8_t *d_flags = nullptr;
-    VT_CHECK(ctx, cudaMalloc(&d_flags, (size_t)nb));
-    int grid = (int)((nb + 127) / 128 < 148 * 32 ? (nb + 127) / 128 : 148 * 32);
-    brick_flags_kernel<<<grid, 128, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[0], ctx->nb[1], ctx->nb[2], d_flags);
-    ctx->launches++;
+    const int G = (ctx->nb[2] + 31) / 32;
+    const long long n_tasks = (long long)ctx->nb[0] * ctx->nb[1] * G;
+    const bool vec = dense_vec(ctx, dev_cells);
+    void *p = nullptr;
+    if (int rc = scene_scratch(ctx, 1, (size_t)n_tasks * 3 * sizeof(uint32_t) + 16, &p)) return rc;
+    unsigned long long *d_total = static_cast<unsigned long long *>(p);
+    uint32_t *d_mask = reinterpret_cast<uint32_t *>(d_total + 2), *d_count = d_mask + n_tasks, *d_base = d_count + n_tasks;
+    if (!ctx->h_word) VT_CHECK(ctx, cudaMallocHost(&ctx->h_word, 64));
+    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
+    long long g1 = (n_tasks + 7) / 8;
+    if (g1 > (long long)sms * 8) g1 = (long long)sms * 8;
+    brick_mask_kernel<<<(int)g1, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G, n_tasks,
+                                                        vec, d_mask, d_count);
+    task_scan_kernel<<<1, 1024, 0, ctx->stream>>>(d_count, n_tasks, d_base, d_total);
+    ctx->launches += 2;
     VT_CHECK(ctx, cudaGetLastError());
-    std::vector<uint8_t> flags((size_t)nb);
-    VT_CHECK(ctx, cudaMemcpyAsync(flags.data(), d_flags, (size_t)nb, cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->h_word, d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_flags);
+    const long long used = (long long)*ctx->h_word;
     ctx->free_slots.clear();
-    long long used = 0;
-    for (long long b = 0; b < nb; b++) ctx->h_brick_tab[(size_t)b] = flags[(size_t)b] ? (uint32_t)(++used) : 0u;
     ctx->pool_used = 0;                                  // nothing to preserve
     if (int rc = grow_pool(ctx, used)) return rc;
     ctx->pool_used = used;
-    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_brick_tab, ctx->h_brick_tab.data(), (size_t)nb * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
-    if (used) {
-        int g2 = (int)(nb < 148 * 64 ? nb : 148 * 64);
-        brick_fill_kernel<<<g2, 512, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], ctx->d_brick_tab, nb, ctx->d_pool);
-        ctx->launches++;
-        VT_CHECK(ctx, cudaGetLastError());
-    }
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    long long g2 = n_tasks < (long long)sms * 8 ? n_tasks : (long long)sms * 8;
+    brick_pack_kernel<<<(int)g2, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G, n_tasks,
+                                                        vec, d_mask, d_base, ctx->d_pool, ctx->d_brick_tab);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));       // the caller may release dev_cells on return
+    ctx->mirror_stale = true;
     return 0;
 }
 
 extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t *dev_cells) {
     if (!ctx || !dev_cells || n < 0 || (n && !objs)) return 1;
     if (!ctx->have_world) return fail(ctx, "vt_build_world: no world (vt_set_world)");
-    for (int k = 0; k < n; k++) {
-        if (!objs[k].dev_sprite) return fail(ctx, "vt_build_world: object without a sprite grid");
-        for (int a = 0; a < 3; a++) {
-            if (objs[k].size[a] <= 0) return fail(ctx, "vt_build_world: sprite size must be positive");
-            if (objs[k].angle[a] < 0 || objs[k].angle[a] > 3) return fail(ctx, "vt_build_world: angle must be 0..3");
-        }
-    }
+    if (int rc = check_objects(ctx, objs, n, "vt_build_world")) return rc;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
     vt_object *d_objs = nullptr;
-    if (n) {
-        VT_CHECK(ctx, cudaMalloc(&d_objs, (size_t)n * sizeof(vt_object)));
-        VT_CHECK(ctx, cudaMemcpyAsync(d_objs, objs, (size_t)n * sizeof(vt_object), cudaMemcpyHostToDevice, ctx->stream));
-    }
-    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ctx->dims[2];
+    if (int rc = stage_objects(ctx, objs, n, &d_objs)) return rc;
+    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ((ctx->dims[2] + 7) / 8);
+    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
     long long want = (total + 255) / 256;
-    int grid = (int)(want < 148LL * 32 ? want : 148LL * 32);
-    build_world_kernel<<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[0],
-                                                      ctx->dims[1], ctx->dims[2], dev_cells);
+    int grid = (int)(want < (long long)sms * 32 ? want : (long long)sms * 32);
+    build_cells_kernel<<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[1], ctx->dims[2], 0, 0,
+                                                      0, ctx->dims[0], ctx->dims[1], ctx->dims[2], dense_vec(ctx, dev_cells), dev_cells);
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_objs);
     return 0;
 }
 
@@ -552,13 +473,7 @@ extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t
 extern "C" int vt_update_region(vt_ctx *ctx, const vt_object *objs, int n, uint8_t *dev_cells, const int32_t lo[3], const int32_t hi[3]) {
     if (!ctx || !dev_cells || !lo || !hi || n < 0 || (n && !objs)) return 1;
     if (!ctx->have_world) return fail(ctx, "vt_update_region: no world (vt_set_world)");
-    for (int k = 0; k < n; k++) {
-        if (!objs[k].dev_sprite) return fail(ctx, "vt_update_region: object without a sprite grid");
-        for (int a = 0; a < 3; a++) {
-            if (objs[k].size[a] <= 0) return fail(ctx, "vt_update_region: sprite size must be positive");
-            if (objs[k].angle[a] < 0 || objs[k].angle[a] > 3) return fail(ctx, "vt_update_region: angle must be 0..3");
-        }
-    }
+    if (int rc = check_objects(ctx, objs, n, "vt_update_region")) return rc;
     int l[3], e[3], b0[3], rb[3];
     for (int a = 0; a < 3; a++) {
         long long p = (long long)lo[a] - ctx->origin[a], q = (long long)hi[a] - ctx->origin[a];
@@ -572,21 +487,22 @@ extern "C" int vt_update_region(vt_ctx *ctx, const vt_object *objs, int n, uint8
         b0[a] = (int)(p / VT_BRICK); rb[a] = (int)((q - p + VT_BRICK - 1) / VT_BRICK);
     }
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (int rc = ensure_mirror(ctx)) return rc;
     const int m = rb[0] * rb[1] * rb[2];
     vt_object *d_objs = nullptr;
-    uint8_t *d_flags = nullptr;
-    uint32_t *d_slots = nullptr;
-    if (n) {
-        VT_CHECK(ctx, cudaMalloc(&d_objs, (size_t)n * sizeof(vt_object)));
-        VT_CHECK(ctx, cudaMemcpyAsync(d_objs, objs, (size_t)n * sizeof(vt_object), cudaMemcpyHostToDevice, ctx->stream));
-    }
-    VT_CHECK(ctx, cudaMalloc(&d_flags, (size_t)m));
-    VT_CHECK(ctx, cudaMalloc(&d_slots, (size_t)m * sizeof(uint32_t)));
-    const long long total = (long long)e[0] * e[1] * e[2];
+    void *p1 = nullptr, *p2 = nullptr;
+    if (int rc = stage_objects(ctx, objs, n, &d_objs)) return rc;
+    if (int rc = scene_scratch(ctx, 1, (size_t)m, &p1)) return rc;
+    if (int rc = scene_scratch(ctx, 2, (size_t)m * sizeof(uint32_t), &p2)) return rc;
+    uint8_t *d_flags = static_cast<uint8_t *>(p1);
+    uint32_t *d_slots = static_cast<uint32_t *>(p2);
+    const long long total = (long long)e[0] * e[1] * ((e[2] + 7) / 8);
+    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
     long long want = (total + 255) / 256;
-    build_region_kernel<<<(int)(want < 148LL * 32 ? want : 148LL * 32), 256, 0, ctx->stream>>>(
-        d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[1], ctx->dims[2], l[0], l[1], l[2], e[0], e[1], e[2], dev_cells);
-    region_flags_kernel<<<(m + 3) / 4 < 148 * 16 ? (m + 3) / 4 : 148 * 16, 128, 0, ctx->stream>>>(
+    build_cells_kernel<<<(int)(want < (long long)sms * 32 ? want : (long long)sms * 32), 256, 0, ctx->stream>>>(
+        d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[1], ctx->dims[2], l[0], l[1], l[2], e[0], e[1], e[2],
+        dense_vec(ctx, dev_cells), dev_cells);
+    region_flags_kernel<<<(m + 3) / 4 < sms * 16 ? (m + 3) / 4 : sms * 16, 128, 0, ctx->stream>>>(
         dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], b0[0], b0[1], b0[2], rb[0], rb[1], rb[2], d_flags);
     ctx->launches += 2;
     VT_CHECK(ctx, cudaGetLastError());
@@ -613,13 +529,50 @@ extern "C" int vt_update_region(vt_ctx *ctx, const vt_object *objs, int n, uint8
     if (int rc = grow_pool(ctx, need)) return rc;
     ctx->pool_used = need;
     VT_CHECK(ctx, cudaMemcpyAsync(d_slots, slots.data(), (size_t)m * sizeof(uint32_t), cudaMemcpyHostToDevice, ctx->stream));
-    region_fill_kernel<<<m < 148 * 8 ? m : 148 * 8, 512, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1],
-                                                                     ctx->nb[2], b0[0], b0[1], b0[2], rb[1], rb[2], d_slots, m,
-                                                                     ctx->d_pool, ctx->d_brick_tab);
+    region_fill_kernel<<<m < sms * 8 ? m : sms * 8, 512, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1],
+                                                                       ctx->nb[2], b0[0], b0[1], b0[2], rb[1], rb[2], d_slots, m,
+                                                                       ctx->d_pool, ctx->d_brick_tab);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));       // `slots` is free on return
+    return 0;
+}
+
+// Bricks -> dense grid in DEVICE memory (the inverse of vt_upload_dense).
+extern "C" int vt_download_dense(vt_ctx *ctx, uint8_t *dev_cells) {
+    if (!ctx || !dev_cells) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_download_dense: no world (vt_set_world)");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ctx->dims[2];
+    long long want = (total + 255) / 256;
+    unpack_cells_kernel<<<(int)(want < 148LL * 32 ? want : 148LL * 32), 256, 0, ctx->stream>>>(ctx->d_brick_tab, ctx->d_pool, ctx->dims[0], ctx->dims[1],
+                                                                                                ctx->dims[2], ctx->nb[1], ctx->nb[2], dev_cells);
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(d_objs); cudaFree(d_flags); cudaFree(d_slots);
+    return 0;
+}
+
+// Chunk slots that hold a voxel (what `post_chunk in self.chunks` answers after chunk_update, init.py:441-452, before
+// LOD / culling), from the brick table: [ncx][ncy][ncz] bytes, z fastest, to HOST memory.  chunk_size % 8 == 0 only.
+extern "C" int vt_chunk_presence(vt_ctx *ctx, uint8_t *host_present, int64_t n_slots) {
+    if (!ctx || !host_present) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_chunk_presence: no world (vt_set_world)");
+    const int cs = ctx->s.chunk_size;
+    if (cs % VT_BRICK != 0) return fail(ctx, "vt_chunk_presence: chunk_size must be a multiple of 8");
+    const long long slots = (long long)ctx->nc[0] * ctx->nc[1] * ctx->nc[2];
+    if (n_slots != slots) return fail(ctx, "vt_chunk_presence: n_slots does not match the world's chunk grid");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    void *p = nullptr;
+    if (int rc = scene_scratch(ctx, 2, (size_t)slots, &p)) return rc;
+    long long want = (slots + 127) / 128;
+    chunk_present_kernel<<<(int)(want < 148LL * 32 ? want : 148LL * 32), 128, 0, ctx->stream>>>(ctx->d_brick_tab, ctx->nb[1], ctx->nb[2], ctx->nc[1],
+                                                                                                 ctx->nc[2], slots, cs / VT_BRICK,
+                                                                                                 static_cast<uint8_t *>(p));
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaMemcpyAsync(host_present, p, (size_t)slots, cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     return 0;
 }
 
