@@ -122,6 +122,8 @@ class WorldBuilder:
         torch.cuda.synchronize(cam.device)
         cam._check(lib.vt_build_world(ctx, arr, len(objects), cells.data_ptr()))
         cam._check(lib.vt_upload_dense(ctx, cells.data_ptr()))
+        cam._dense_mode = True
+        cam.chunks = {}
         cam._world_origin = origin
         cam._world_shape = tuple(int(v) for v in dims)
         if cs % 8 == 0:
@@ -132,8 +134,6 @@ class WorldBuilder:
         self.cells, self.origin = cells, origin
         self.order = list(objects)
         self.drawn = {id(o): chunk_box(o, cs) for o in objects}
-        cam._dense_mode = True
-        cam.chunks = {}
         cam._static_materials = np.ascontiguousarray(materials, dtype=np.float64)
         self.update_lod(visible=None)
         return cells
@@ -193,10 +193,13 @@ class WorldBuilder:
             cam._check(cam._lib.vt_update_region(cam._ctx, arr, len(self.order), self.cells.data_ptr(), l3, h3))
             c0 = [(lo[a] - lo_w[a]) // cs for a in range(3)]
             c1 = [(hi[a] - lo_w[a]) // cs for a in range(3)]
-            sub = self.cells[c0[0] * cs:c1[0] * cs, c0[1] * cs:c1[1] * cs, c0[2] * cs:c1[2] * cs]
-            pres = sub.reshape(c1[0] - c0[0], cs, c1[1] - c0[1], cs, c1[2] - c0[2], cs).amax(dim=(1, 3, 5)).ne(0).cpu().numpy()
-            self.present[c0[0]:c1[0], c0[1]:c1[1], c0[2]:c1[2]] = pres
+            if cs % 8 != 0:
+                sub = self.cells[c0[0] * cs:c1[0] * cs, c0[1] * cs:c1[1] * cs, c0[2] * cs:c1[2] * cs]
+                pres = sub.reshape(c1[0] - c0[0], cs, c1[1] - c0[1], cs, c1[2] - c0[2], cs).amax(dim=(1, 3, 5)).ne(0).cpu().numpy()
+                self.present[c0[0]:c1[0], c0[1]:c1[1], c0[2]:c1[2]] = pres
             n_chunks += int(np.prod([c1[a] - c0[a] for a in range(3)]))
+        if cs % 8 == 0:
+            self.present = cam.chunk_presence()                # one small kernel over the brick table + 1 byte per chunk D2H
         return n_chunks
 
     def update_lod(self, visible=None):

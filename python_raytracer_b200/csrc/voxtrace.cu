@@ -66,6 +66,7 @@ struct vt_ctx {
     uint8_t *d_chunk_res = nullptr;
     uint32_t *d_brick_tab = nullptr;
     std::vector<uint32_t> h_brick_tab;          // host mirror: 0 = empty else slot + 1
+    int world_cs = 0;                           // chunk_size the chunk table was sized for
     bool mirror_stale = false;                  // vt_upload_dense numbered the slots on the device: mirror not fetched yet
     // scene-building scratch (grow-only device buffers) and one pinned word for the device-side brick count
     void *scene_buf[3] = {nullptr, nullptr, nullptr}; size_t scene_cap[3] = {0, 0, 0};
@@ -264,17 +265,27 @@ extern "C" int vt_set_world(vt_ctx *ctx, const int32_t origin[3], const int32_t 
     }
     if (bricks > (1LL << 31) || slots > (1LL << 31)) return fail(ctx, "vt_set_world: world too large");
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    free_world(ctx);
+    // The brick pool is kept across worlds (its contents are dropped, its memory is reused: a rebuild packs into it
+    // without waiting for the brick count) and so are the tables when the box has the same shape.
+    bool same = ctx->have_world && ctx->world_cs == cs;
+    for (int a = 0; a < 3; a++) same = same && ctx->dims[a] == dims[a];
+    if (!same) {
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+        cudaFree(ctx->d_chunk_res); cudaFree(ctx->d_brick_tab);
+        ctx->d_chunk_res = nullptr; ctx->d_brick_tab = nullptr;
+        ctx->have_world = false;
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_chunk_res, (size_t)slots));
+        VT_CHECK(ctx, cudaMalloc(&ctx->d_brick_tab, (size_t)bricks * sizeof(uint32_t)));
+    }
     for (int a = 0; a < 3; a++) {
         ctx->origin[a] = origin[a]; ctx->dims[a] = dims[a];
         ctx->nb[a] = (dims[a] + VT_BRICK - 1) / VT_BRICK; ctx->nc[a] = dims[a] / cs;
     }
-    VT_CHECK(ctx, cudaMalloc(&ctx->d_chunk_res, (size_t)slots));
     VT_CHECK(ctx, cudaMemsetAsync(ctx->d_chunk_res, 0, (size_t)slots, ctx->stream));
-    VT_CHECK(ctx, cudaMalloc(&ctx->d_brick_tab, (size_t)bricks * sizeof(uint32_t)));
     VT_CHECK(ctx, cudaMemsetAsync(ctx->d_brick_tab, 0, (size_t)bricks * sizeof(uint32_t), ctx->stream));
     ctx->h_brick_tab.assign((size_t)bricks, 0u);
+    ctx->pool_used = 0; ctx->free_slots.clear(); ctx->mirror_stale = false;
+    ctx->max_res = 0; ctx->world_cs = cs;
     ctx->have_world = true;
     return 0;
 }
@@ -431,19 +442,30 @@ extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
     task_scan_kernel<<<1, 1024, 0, ctx->stream>>>(d_count, n_tasks, d_base, d_total);
     ctx->launches += 2;
     VT_CHECK(ctx, cudaGetLastError());
+    const long long g2 = n_tasks < (long long)sms * 8 ? n_tasks : (long long)sms * 8;
+    // A pool exists already (re-upload, or bricks uploaded before): pack into it right away and look at the count
+    // afterwards -- the pass is repeated only if the pool turns out to be too small.  No pool yet: count first.
+    const bool optimistic = ctx->pool_cap > 0;
+    if (optimistic) {
+        brick_pack_kernel<<<(int)g2, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G,
+                                                            n_tasks, vec, d_mask, d_base, (uint32_t)ctx->pool_cap, ctx->d_pool, ctx->d_brick_tab);
+        ctx->launches++;
+        VT_CHECK(ctx, cudaGetLastError());
+    }
     VT_CHECK(ctx, cudaMemcpyAsync(ctx->h_word, d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));       // also: the caller may release dev_cells on return
     const long long used = (long long)*ctx->h_word;
     ctx->free_slots.clear();
-    ctx->pool_used = 0;                                  // nothing to preserve
-    if (int rc = grow_pool(ctx, used)) return rc;
+    ctx->pool_used = 0;                                      // nothing to preserve
+    if (!optimistic || used > ctx->pool_cap) {
+        if (int rc = grow_pool(ctx, used)) return rc;
+        brick_pack_kernel<<<(int)g2, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G,
+                                                            n_tasks, vec, d_mask, d_base, (uint32_t)ctx->pool_cap, ctx->d_pool, ctx->d_brick_tab);
+        ctx->launches++;
+        VT_CHECK(ctx, cudaGetLastError());
+        VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    }
     ctx->pool_used = used;
-    long long g2 = n_tasks < (long long)sms * 8 ? n_tasks : (long long)sms * 8;
-    brick_pack_kernel<<<(int)g2, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G, n_tasks,
-                                                        vec, d_mask, d_base, ctx->d_pool, ctx->d_brick_tab);
-    ctx->launches++;
-    VT_CHECK(ctx, cudaGetLastError());
-    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));       // the caller may release dev_cells on return
     ctx->mirror_stale = true;
     return 0;
 }
@@ -543,10 +565,11 @@ extern "C" int vt_download_dense(vt_ctx *ctx, uint8_t *dev_cells) {
     if (!ctx || !dev_cells) return 1;
     if (!ctx->have_world) return fail(ctx, "vt_download_dense: no world (vt_set_world)");
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ctx->dims[2];
+    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ((ctx->dims[2] + 7) / 8);
     long long want = (total + 255) / 256;
     unpack_cells_kernel<<<(int)(want < 148LL * 32 ? want : 148LL * 32), 256, 0, ctx->stream>>>(ctx->d_brick_tab, ctx->d_pool, ctx->dims[0], ctx->dims[1],
-                                                                                                ctx->dims[2], ctx->nb[1], ctx->nb[2], dev_cells);
+                                                                                                ctx->dims[2], ctx->nb[1], ctx->nb[2],
+                                                                                                dense_vec(ctx, dev_cells), dev_cells);
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));

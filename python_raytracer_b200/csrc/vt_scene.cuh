@@ -59,12 +59,21 @@ __device__ __forceinline__ void pos_rotated(const vt_object &o, int &x, int &y, 
     }
 }
 
+// 0xff in every byte of the result whose byte in v is not zero
+__device__ __forceinline__ unsigned long long nonzero_bytes(unsigned long long v) {
+    const unsigned long long lo7 = 0x7f7f7f7f7f7f7f7full;
+    unsigned long long t = (((v & lo7) + lo7) | v) & ~lo7;               // 0x80 where the byte is non-zero
+    return t | (t - (t >> 7));
+}
+
 // Window.chunk_update's voxel gathering (init.py:413-424, 437-439) for the eight world cells (wx, wy, wz0 .. wz0 + 7):
 // the last object in list order that has a voxel at a cell wins.  Objects are tested against the whole run first
-// (point test in x and y, interval overlap in z); only the cells still empty are looked up in the next object.
+// (point test in x and y, interval overlap in z); only the cells still empty are taken from the next object.
+// `need` holds 0xff for every cell that is still empty.  An unrotated object whose box covers the whole run gives
+// its eight cells with two aligned 8-byte loads and a funnel shift (sprite rows start at any byte); everything else
+// -- rotations, runs that straddle the box, the last bytes of a sprite -- goes cell by cell.
 __device__ __forceinline__ uint2 gather_run8(const vt_object *__restrict__ objs, int n, int wx, int wy, int wz0) {
-    uint32_t out[2] = {0u, 0u};
-    uint32_t need = 0xffu;
+    unsigned long long out = 0ull, need = ~0ull;
     for (int k = n - 1; k >= 0 && need; k--) {
         const vt_object &o = objs[k];
         if (wx < o.mins[0] || wx >= o.maxs[0] || wy < o.mins[1] || wy >= o.maxs[1]) continue;
@@ -72,17 +81,32 @@ __device__ __forceinline__ uint2 gather_run8(const vt_object *__restrict__ objs,
         if (c0 >= c1) continue;
         const bool plain = (o.angle[0] | o.angle[1] | o.angle[2]) == 0;
         const int bx = wx - o.mins[0], by = wy - o.mins[1], bz = wz0 - o.mins[2];
+        const int s0 = o.size[0], s1 = o.size[1], s2 = o.size[2];
+        if (plain && c0 == 0 && c1 == 8 && (unsigned)bx < (unsigned)s0 && (unsigned)by < (unsigned)s1 && bz >= 0 && bz + 8 <= s2 &&
+            (reinterpret_cast<uintptr_t>(o.dev_sprite) & 7u) == 0) {
+            const size_t off = ((size_t)bx * s1 + by) * s2 + bz;
+            if (off + 16 <= (size_t)s0 * s1 * s2) {                       // both aligned words lie inside the sprite
+                const unsigned long long *p = reinterpret_cast<const unsigned long long *>(o.dev_sprite + (off & ~(size_t)7));
+                const int sh = (int)(off & 7) * 8;
+                unsigned long long v = __ldg(p);
+                if (sh) v = (v >> sh) | (__ldg(p + 1) << (64 - sh));
+                const unsigned long long m = nonzero_bytes(v) & need;
+                out |= v & m;
+                need &= ~m;
+                continue;
+            }
+        }
 #pragma unroll
         for (int c = 0; c < 8; c++) {
-            if (c < c0 || c >= c1 || !((need >> c) & 1u)) continue;
+            if (c < c0 || c >= c1 || !((need >> (8 * c)) & 1ull)) continue;
             int lx = bx, ly = by, lz = bz + c;
             if (!plain) pos_rotated(o, lx, ly, lz);
-            if ((unsigned)lx >= (unsigned)o.size[0] || (unsigned)ly >= (unsigned)o.size[1] || (unsigned)lz >= (unsigned)o.size[2]) continue;
-            const uint32_t m = __ldg(o.dev_sprite + ((size_t)lx * o.size[1] + ly) * o.size[2] + lz);
-            if (m) { out[c >> 2] |= m << (8 * (c & 3)); need &= ~(1u << c); }
+            if ((unsigned)lx >= (unsigned)s0 || (unsigned)ly >= (unsigned)s1 || (unsigned)lz >= (unsigned)s2) continue;
+            const unsigned long long m = __ldg(o.dev_sprite + ((size_t)lx * s1 + ly) * s2 + lz);
+            if (m) { out |= m << (8 * c); need &= ~(0xffull << (8 * c)); }
         }
     }
-    return make_uint2(out[0], out[1]);
+    return make_uint2((uint32_t)out, (uint32_t)(out >> 32));
 }
 
 // Cells of the box [l, l + e) of the dense grid [..][ny][nz] (the whole world: l = 0, e = dims), one thread per run
@@ -135,12 +159,24 @@ __global__ void __launch_bounds__(256) brick_mask_kernel(const uint8_t *__restri
         const int bz = g * 32 + lane, z0 = bz * 8;
         uint32_t acc = 0;
         if (bz < nbz) {
-#pragma unroll 8
-            for (int r = 0; r < 64; r++) {
-                const int x = bx * 8 + (r >> 3), y = by * 8 + (r & 7);
-                if (x < nx && y < ny) {
-                    const uint2 v = load_run8(dense + ((size_t)x * ny + y) * nz, z0, nz, vec);
-                    acc |= v.x | v.y;
+            if (vec && bx * 8 + 8 <= nx && by * 8 + 8 <= ny) {            // interior column: eight independent loads in flight
+                const uint2 *p = reinterpret_cast<const uint2 *>(dense + ((size_t)(bx * 8) * ny + by * 8) * nz + z0);
+                const size_t sy = (size_t)nz >> 3, sx = sy * ny;
+#pragma unroll 2
+                for (int lx = 0; lx < 8; lx++) {
+                    uint2 v[8];
+#pragma unroll
+                    for (int ly = 0; ly < 8; ly++) v[ly] = __ldg(p + lx * sx + ly * sy);
+#pragma unroll
+                    for (int ly = 0; ly < 8; ly++) acc |= v[ly].x | v[ly].y;
+                }
+            } else {
+                for (int r = 0; r < 64; r++) {
+                    const int x = bx * 8 + (r >> 3), y = by * 8 + (r & 7);
+                    if (x < nx && y < ny) {
+                        const uint2 v = load_run8(dense + ((size_t)x * ny + y) * nz, z0, nz, vec);
+                        acc |= v.x | v.y;
+                    }
                 }
             }
         }
@@ -149,7 +185,8 @@ __global__ void __launch_bounds__(256) brick_mask_kernel(const uint8_t *__restri
     }
 }
 
-// Exclusive scan of count[0 .. n) by one block of 1024 threads; *total = sum.  (n = bricks / 32: 8 192 for a 512^3 world.)
+// Exclusive scan of count[0 .. n) by one block of 1024 threads, eight consecutive entries per thread; *total = sum.
+// (n = bricks / 32: 8 192 for a 512^3 world, i.e. one pass of the loop.)
 __global__ void __launch_bounds__(1024) task_scan_kernel(const uint32_t *__restrict__ count, long long n, uint32_t *__restrict__ base,
                                                          unsigned long long *__restrict__ total) {
     __shared__ uint32_t wsum[32];
@@ -157,10 +194,14 @@ __global__ void __launch_bounds__(1024) task_scan_kernel(const uint32_t *__restr
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     unsigned long long carry = 0;
-    for (long long i0 = 0; i0 < n; i0 += 1024) {
-        const long long i = i0 + threadIdx.x;
-        const uint32_t v = i < n ? count[i] : 0u;
-        uint32_t s = v;
+    for (long long i0 = 0; i0 < n; i0 += 8192) {
+        const long long i = i0 + 8 * threadIdx.x;
+        uint32_t v[8], mine = 0;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { v[k] = i + k < n ? count[i + k] : 0u; }
+#pragma unroll
+        for (int k = 0; k < 8; k++) mine += v[k];
+        uint32_t s = mine;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) { const uint32_t u = __shfl_up_sync(full, s, d); if (lane >= d) s += u; }
         if (lane == 31) wsum[w] = s;
@@ -174,7 +215,9 @@ __global__ void __launch_bounds__(1024) task_scan_kernel(const uint32_t *__restr
             if (lane == 31) chunk_sum = q;
         }
         __syncthreads();
-        if (i < n) base[i] = (uint32_t)carry + wsum[w] + s - v;
+        uint32_t run = (uint32_t)carry + wsum[w] + s - mine;
+#pragma unroll
+        for (int k = 0; k < 8; k++) { if (i + k < n) base[i + k] = run; run += v[k]; }
         carry += chunk_sum;
         __syncthreads();
     }
@@ -185,11 +228,14 @@ __global__ void __launch_bounds__(1024) task_scan_kernel(const uint32_t *__restr
 // (rows padded by 8 bytes against bank conflicts), then every non-empty brick is written to its pool slot as
 // 32 lanes x 16 bytes = 512 contiguous bytes: pool index (lx * 8 + ly) * 8 + lz = row * 8 + lz, so 16 bytes are the
 // runs of rows 2k and 2k + 1.  Warp 0 also writes the task's 32 brick-table entries (0 = empty, else slot + 1).
+// The host launches this pass before it knows the brick count when a pool already exists (no host round trip in the
+// middle of the pipeline): bricks whose slot lies beyond `pool_cap` are skipped and the pass is repeated after the
+// pool has grown.
 #define VT_PACK_ROW 264
 __global__ void __launch_bounds__(256) brick_pack_kernel(const uint8_t *__restrict__ dense, int nx, int ny, int nz, int nby, int nbz, int G,
                                                          long long n_tasks, bool vec, const uint32_t *__restrict__ task_mask,
-                                                         const uint32_t *__restrict__ task_base, uint8_t *__restrict__ pool,
-                                                         uint32_t *__restrict__ brick_tab) {
+                                                         const uint32_t *__restrict__ task_base, uint32_t pool_cap,
+                                                         uint8_t *__restrict__ pool, uint32_t *__restrict__ brick_tab) {
     __shared__ __align__(16) uint8_t tile[64 * VT_PACK_ROW];
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     for (long long t = blockIdx.x; t < n_tasks; t += gridDim.x) {
@@ -215,6 +261,7 @@ __global__ void __launch_bounds__(256) brick_pack_kernel(const uint8_t *__restri
         for (int j = w; j < 32; j += 8) {
             if (!((mask >> j) & 1u)) continue;                            // warp-uniform
             const uint32_t slot = base + (uint32_t)__popc(mask & ((1u << j) - 1u));
+            if (slot >= pool_cap) continue;                               // optimistic launch into a pool that is too small: redone by the host
             const uint2 a = *reinterpret_cast<const uint2 *>(tile + (2 * lane) * VT_PACK_ROW + 8 * j);
             const uint2 b = *reinterpret_cast<const uint2 *>(tile + (2 * lane + 1) * VT_PACK_ROW + 8 * j);
             reinterpret_cast<uint4 *>(pool + (size_t)slot * 512u)[lane] = make_uint4(a.x, a.y, b.x, b.y);
@@ -238,14 +285,18 @@ __global__ void chunk_present_kernel(const uint32_t *__restrict__ brick_tab, int
 }
 
 // Inverse of the pack pass: bricks -> dense [nx][ny][nz] grid (read-back for checks and for callers that switch from
-// the chunk_set path to the dense path); one thread per cell.
-__global__ void unpack_cells_kernel(const uint32_t *__restrict__ brick_tab, const uint8_t *__restrict__ pool, int nx, int ny, int nz, int nby,
-                                    int nbz, uint8_t *__restrict__ dense) {
-    const long long total = (long long)nx * ny * nz;
+// the chunk_set path to the dense path); one thread per run of eight cells = one 8-byte row of a brick.
+__global__ void __launch_bounds__(256) unpack_cells_kernel(const uint32_t *__restrict__ brick_tab, const uint8_t *__restrict__ pool, int nx, int ny,
+                                                           int nz, int nby, int nbz, bool vec, uint8_t *__restrict__ dense) {
+    const int runs = (nz + 7) >> 3;
+    const long long total = (long long)nx * ny * runs;
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-        const int z = (int)(i % nz), y = (int)((i / nz) % ny), x = (int)(i / ((long long)nz * ny));
-        const uint32_t b = __ldg(&brick_tab[((size_t)(x >> 3) * nby + (y >> 3)) * nbz + (z >> 3)]);
-        dense[i] = b ? __ldg(&pool[(size_t)(b - 1u) * 512u + (((x & 7) << 6) | ((y & 7) << 3) | (z & 7))]) : 0;
+        const long long row = i / runs;
+        const int r = (int)(i - row * runs), x = (int)(row / ny), y = (int)(row - (long long)x * ny);
+        const uint32_t b = __ldg(&brick_tab[((size_t)(x >> 3) * nby + (y >> 3)) * nbz + r]);
+        uint2 v = make_uint2(0u, 0u);
+        if (b) v = __ldg(reinterpret_cast<const uint2 *>(pool + (size_t)(b - 1u) * 512u + (((x & 7) << 6) | ((y & 7) << 3))));
+        store_run8(dense + ((size_t)x * ny + y) * nz, 8 * r, nz, vec, v);
     }
 }
 

@@ -60,6 +60,12 @@ def test_pack_roundtrip_count_and_presence(cs, dims):
     cam.set_world_dense(origin, cells2, res, MATS)
     assert np.array_equal(cam.download_dense().cpu().numpy(), cells2)
     assert cam.world_stats()["bricks"] == _brick_count(cells2)
+    # a denser world into the existing pool: the pack pass is launched before the count is known and repeated when
+    # the pool turns out to be too small (the 48 x 32 x 512 case: 1 536 bricks into a pool of 1 024)
+    cells3 = _random_world(dims, seed=9, fill=0.5, holes=False)
+    cam.set_world_dense(origin, cells3, res, MATS)
+    assert np.array_equal(cam.download_dense().cpu().numpy(), cells3)
+    assert cam.world_stats()["bricks"] == _brick_count(cells3)
     cam.close()
 
 
