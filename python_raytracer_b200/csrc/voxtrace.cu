@@ -420,20 +420,16 @@ extern "C" int vt_upload_bricks(vt_ctx *ctx, const int32_t *coords, const uint8_
 
 // Dense world -> brick pool + brick table, entirely on the device: occupancy bits (one pass over the cells), an
 // exclusive scan of the per-task counts (slots in brick-index order), then the pack pass (second read of the cells,
-// mostly from L2 for worlds below ~100 MiB; one 512-byte store per non-empty brick).  The only host step is reading
-// the brick COUNT back (8 bytes, pinned) to size the pool.
-extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
-    if (!ctx || !dev_cells) return 1;
-    if (!ctx->have_world) return fail(ctx, "vt_upload_dense: no world (vt_set_world)");
-    VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    const int G = (ctx->nb[2] + 31) / 32;
-    const long long n_tasks = (long long)ctx->nb[0] * ctx->nb[1] * G;
-    const bool vec = dense_vec(ctx, dev_cells);
+// partly from L2; one 512-byte store per non-empty brick).  The only host step is reading the brick COUNT back
+// (8 bytes, pinned) -- after the pack pass when a pool exists already (the pass is repeated if the pool turns out too
+// small).  A single-pass variant (occupancy, slot numbering by decoupled look-back and the stores in one kernel, the
+// grid read once) was measured and lost: 123-129 us against 67 us for the three kernels on the 512^3 terrain -- the
+// look-back chain over 8 192 tasks costs more than the second, L2-assisted read.
+static int upload_dense_split(vt_ctx *ctx, const uint8_t *dev_cells, int G, long long n_tasks, bool vec) {
     void *p = nullptr;
     if (int rc = scene_scratch(ctx, 1, (size_t)n_tasks * 3 * sizeof(uint32_t) + 16, &p)) return rc;
     unsigned long long *d_total = static_cast<unsigned long long *>(p);
     uint32_t *d_mask = reinterpret_cast<uint32_t *>(d_total + 2), *d_count = d_mask + n_tasks, *d_base = d_count + n_tasks;
-    if (!ctx->h_word) VT_CHECK(ctx, cudaMallocHost(&ctx->h_word, 64));
     const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
     long long g1 = (n_tasks + 7) / 8;
     if (g1 > (long long)sms * 8) g1 = (long long)sms * 8;
@@ -443,8 +439,6 @@ extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
     ctx->launches += 2;
     VT_CHECK(ctx, cudaGetLastError());
     const long long g2 = n_tasks < (long long)sms * 8 ? n_tasks : (long long)sms * 8;
-    // A pool exists already (re-upload, or bricks uploaded before): pack into it right away and look at the count
-    // afterwards -- the pass is repeated only if the pool turns out to be too small.  No pool yet: count first.
     const bool optimistic = ctx->pool_cap > 0;
     if (optimistic) {
         brick_pack_kernel<<<(int)g2, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G,
@@ -455,8 +449,6 @@ extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
     VT_CHECK(ctx, cudaMemcpyAsync(ctx->h_word, d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));       // also: the caller may release dev_cells on return
     const long long used = (long long)*ctx->h_word;
-    ctx->free_slots.clear();
-    ctx->pool_used = 0;                                      // nothing to preserve
     if (!optimistic || used > ctx->pool_cap) {
         if (int rc = grow_pool(ctx, used)) return rc;
         brick_pack_kernel<<<(int)g2, 256, 0, ctx->stream>>>(dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], ctx->nb[1], ctx->nb[2], G,
@@ -466,6 +458,20 @@ extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
         VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
     }
     ctx->pool_used = used;
+    return 0;
+}
+
+extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
+    if (!ctx || !dev_cells) return 1;
+    if (!ctx->have_world) return fail(ctx, "vt_upload_dense: no world (vt_set_world)");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    const int G = (ctx->nb[2] + 31) / 32;
+    const long long n_tasks = (long long)ctx->nb[0] * ctx->nb[1] * G;
+    const bool vec = dense_vec(ctx, dev_cells);
+    if (!ctx->h_word) VT_CHECK(ctx, cudaMallocHost(&ctx->h_word, 64));
+    ctx->free_slots.clear();
+    ctx->pool_used = 0;                                      // nothing to preserve
+    if (int rc = upload_dense_split(ctx, dev_cells, G, n_tasks, vec)) return rc;
     ctx->mirror_stale = true;
     return 0;
 }
