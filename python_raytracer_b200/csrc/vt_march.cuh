@@ -16,6 +16,23 @@
 #pragma once
 #include "vt_device.cuh"
 
+// Compile-time switches (tools/build_variants.py); they must precede their first use.
+#ifndef VT_MARCH_KEEP
+#define VT_MARCH_KEEP 1             // the march phase goes on while >= KEEP/8 of the lanes that entered it still march
+#endif
+#ifndef VT_TRIPS           // dev instrumentation (tools/kbench.py KB_COUNTERS): phase trip counts in counters[8..13]
+#define VT_TRIPS 0
+#endif
+#ifndef VT_LODLOOP
+#define VT_LODLOOP 0                 // per-lane loop inside LOD chunks: measured, no gain (C4 +1 %, bench +0.3 %), off
+#endif
+#ifndef VT_LOOP2
+#define VT_LOOP2 1                   // brick-local loop in two specialised copies (empty / non-empty brick)
+#endif
+#ifndef VT_MINB
+#define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
+#endif
+
 namespace vt {
 
 enum : uint32_t { ST_NONE = 0u, ST_MARCH = 1u, ST_HIT = 2u, ST_DONE = 3u };
@@ -266,8 +283,37 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
                 // state machine; the sample positions themselves are the reference's, one fp64 add per axis per sample.
                 // The world origin is a multiple of 8 here, so brick membership is tested on absolute cells.
                 if (L.res == 1 && P.brick_runs && VT_IN(b <= w.pool_slots, 5)) {
-                    const uint8_t *pb = w.pool + (size_t)(b ? b - 1u : 0u) * 512u;
                     const int ax = ix + w.ox, ay = iy + w.oy, az = iz + w.oz;
+#if VT_LOOP2
+                    // Two specialised loops.  Empty brick: nothing to load, the loop is the position update, the
+                    // life test, three floors and the same-brick test.  Non-empty brick: the cell index is taken
+                    // relative to the brick's corner -- jx * 64 + jy * 8 + jz minus the same expression of the corner,
+                    // in wrapping 32-bit arithmetic (the true difference is 0..511) -- instead of three masks, two
+                    // shifts and two ors per sample.
+                    if (!b) {
+                        for (;;) {
+                            L.step += 1.0;
+                            L.px += L.vx; L.py += L.vy; L.pz += L.vz;   // vel * 1.0 == vel
+                            if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
+                            const int jx = floor_i(L.px), jy = floor_i(L.py), jz = floor_i(L.pz);
+                            if ((((jx ^ ax) | (jy ^ ay) | (jz ^ az)) & ~7) != 0) return;      // next sample: another brick
+                            if (COUNT) c.in_chunk++;
+                        }
+                    }
+                    const uint8_t *pb = w.pool + (size_t)(b - 1u) * 512u;
+                    const uint32_t corner = ((uint32_t)(ax & ~7) << 6) + ((uint32_t)(ay & ~7) << 3) + (uint32_t)(az & ~7);
+                    mat = __ldg(pb + ((((uint32_t)ax << 6) + ((uint32_t)ay << 3) + (uint32_t)az) - corner));
+                    while (!mat) {
+                        L.step += 1.0;
+                        L.px += L.vx; L.py += L.vy; L.pz += L.vz;
+                        if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
+                        const int jx = floor_i(L.px), jy = floor_i(L.py), jz = floor_i(L.pz);
+                        if ((((jx ^ ax) | (jy ^ ay) | (jz ^ az)) & ~7) != 0) return;
+                        if (COUNT) c.in_chunk++;
+                        mat = __ldg(pb + ((((uint32_t)jx << 6) + ((uint32_t)jy << 3) + (uint32_t)jz) - corner));
+                    }
+#else
+                    const uint8_t *pb = w.pool + (size_t)(b ? b - 1u : 0u) * 512u;
                     if (b) mat = __ldg(pb + (((ix & 7) << 6) | ((iy & 7) << 3) | (iz & 7)));
                     while (!mat) {
                         L.step += 1.0;
@@ -278,6 +324,7 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
                         if (COUNT) c.in_chunk++;
                         if (b) mat = __ldg(pb + (((jx & 7) << 6) | ((jy & 7) << 3) | (jz & 7)));
                     }
+#endif
                 } else if (b && VT_IN(b <= w.pool_slots, 5))
                     mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
             }
@@ -544,19 +591,6 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
     int ix = floor_i(L.px) - P.w.ox, iy = floor_i(L.py) - P.w.oy, iz = floor_i(L.pz) - P.w.oz;
     if (!rechunk<FAST, FULL_TAIL, COUNT>(P, L, ix, iy, iz, c)) lane_set_state(L, ST_DONE);
 }
-
-#ifndef VT_MARCH_KEEP
-#define VT_MARCH_KEEP 1             // the march phase goes on while >= KEEP/8 of the lanes that entered it still march
-#endif
-#ifndef VT_TRIPS           // dev instrumentation (tools/kbench.py KB_COUNTERS): phase trip counts in counters[8..13]
-#define VT_TRIPS 0
-#endif
-#ifndef VT_LODLOOP
-#define VT_LODLOOP 1
-#endif
-#ifndef VT_MINB
-#define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
-#endif
 
 // Camera.tile (reference init.py:126-150) for a whole region: one persistent launch.
 template <bool FAST, bool REC, bool FULL_TAIL, bool COUNT>

@@ -52,6 +52,8 @@ for yaw in (0.0, 90.0, 180.0, 270.0):
                    hits_per_ray=round(cnt[3] / cnt[0], 3)))
 res["c4"] = dict(frames=c4, bricks=st["bricks"], world_bytes=st["bytes"], dense_bytes=int(cells.size), h2d_s=round(t1 - t0, 4), brick_s=round(t2 - t1, 4))
 cam.close(); del dev_cells
+if os.environ.get("ST_ONLY") == "c4":                    # quick A/B of kernel variants on the terrain (VT_LIB=...)
+    print(json.dumps(res)); sys.exit(0)
 # ---- C5
 sd = dict(C5_SETTINGS); sd["threads"] = 1
 size = (512, 256, 512)
