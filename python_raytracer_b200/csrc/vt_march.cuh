@@ -29,6 +29,9 @@
 #ifndef VT_LOOP2
 #define VT_LOOP2 1                   // brick-local loop in two specialised copies (empty / non-empty brick)
 #endif
+#ifndef VT_SINCOS_SMALL
+#define VT_SINCOS_SMALL 1            // sin / cos of the half lens angles without argument reduction when |a| <= pi/4
+#endif
 #ifndef VT_MINB
 #define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
 #endif
@@ -72,6 +75,33 @@ __device__ __noinline__ uint4 philox_block(uint32_t block, uint32_t sample, uint
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
 __device__ __noinline__ double2 sincos_out(double a) {
+#if VT_SINCOS_SMALL
+    // Half lens angles are small (fov 90: |a| < 0.41 rad): below pi/4 no argument reduction and no quadrant logic are
+    // needed, sin and cos are two Horner chains of explicit FMAs (Taylor to a^17 / a^16, truncation < 1e-19 at pi/4;
+    // within 1 ulp of libm like libdevice's own sincos, which parity tolerates -- DESIGN.md section 4, Numerics).
+    if (fabs(a) <= 0.78539816339744830962) {
+        const double z = a * a;
+        double p = 2.81145725434552076320e-15;                                  //  1 / 17!
+        p = __fma_rn(p, z, -7.64716373181981647590e-13);                       // -1 / 15!
+        p = __fma_rn(p, z, 1.60590438368216145994e-10);                        //  1 / 13!
+        p = __fma_rn(p, z, -2.50521083854417187751e-08);                       // -1 / 11!
+        p = __fma_rn(p, z, 2.75573192239858906526e-06);                        //  1 / 9!
+        p = __fma_rn(p, z, -1.98412698412698412698e-04);                       // -1 / 7!
+        p = __fma_rn(p, z, 8.33333333333333333333e-03);                        //  1 / 5!
+        p = __fma_rn(p, z, -1.66666666666666666667e-01);                       // -1 / 3!
+        const double s = __fma_rn(a * z, p, a);
+        double q = 4.77947733238738529744e-14;                                  //  1 / 16!
+        q = __fma_rn(q, z, -1.14707455977297247139e-11);                       // -1 / 14!
+        q = __fma_rn(q, z, 2.08767569878680989792e-09);                        //  1 / 12!
+        q = __fma_rn(q, z, -2.75573192239858906526e-07);                       // -1 / 10!
+        q = __fma_rn(q, z, 2.48015873015873015873e-05);                        //  1 / 8!
+        q = __fma_rn(q, z, -1.38888888888888888889e-03);                       // -1 / 6!
+        q = __fma_rn(q, z, 4.16666666666666666667e-02);                        //  1 / 4!
+        const double hz = 0.5 * z, w = 1.0 - hz;                               // 1 - z/2 with its rounding error fed back
+        const double c = w + (((1.0 - w) - hz) + (z * z) * q);
+        return make_double2(s, c);
+    }
+#endif
     double s, c;
     sincos(a, &s, &c);
     return make_double2(s, c);
