@@ -821,6 +821,11 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
     P.total_rays = (unsigned long long)P.n_warps * (unsigned long long)P.rounds * 32ull;
     if ((P.total_rays >> 5) > 0xffffffffull) return fail(ctx, "vt_render: region too large for one launch");
     P.acc_wide = smax > 64 ? 1 : 0;
+    // lod_edge == 0: every pixel has n = max(1, samples) samples; for a power of two the mean x / n is x * (1 / n) exactly
+    {
+        const long long n = s.samples < 1 ? 1 : s.samples;
+        P.inv_samples = (s.lod_edge == 0.0 && (n & (n - 1)) == 0) ? 1.0 / (double)n : 0.0;
+    }
     long long words = P.n_pixels * (P.acc_wide ? 2 : 1);
     if (words > ctx->acc_cap) {
         VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));

@@ -76,6 +76,7 @@ struct DevParams {
     unsigned int total_warps;       // warps launched
     int refill_min;                 // refill once this many lanes are idle
     unsigned long long *pow_tab;    // [VT_POW_SLOTS][2] {bits of x, bits of pow(x, 1 + falloff)} filled as values occur; 0 = empty
+    double inv_samples;             // 1 / n when every pixel has the same power-of-two sample count n (exact mean), else 0
     int brick_runs;                 // 1: chunk_size % 8 == 0, empty-brick runs allowed (VT_RUNS=0 disables, A/B)
     uint32_t lod_magic[VT_LOD_TAB + 1];   // floor(n / r) == umulhi(n, magic[r]) for n < 2^24 / r ... (r >= 2)
     int32_t lod_bias[VT_LOD_TAB + 1][3];  // world origin mod r per axis

@@ -32,6 +32,9 @@
 #ifndef VT_SINCOS_SMALL
 #define VT_SINCOS_SMALL 1            // sin / cos of the half lens angles without argument reduction when |a| <= pi/4
 #endif
+#ifndef VT_INVN
+#define VT_INVN 1                    // pixel mean by an exact reciprocal multiply when the sample count is a power of two
+#endif
 #ifndef VT_MINB
 #define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
 #endif
@@ -539,8 +542,14 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
         }
     }
     if (last) {
-        double dn = i2d(n);
-        double mr = u2d((uint32_t)sr) / dn, mg = u2d((uint32_t)sg) / dn, mb = u2d((uint32_t)sb) / dn, ma = u2d((uint32_t)sa) / dn;
+        double mr, mg, mb, ma;
+        if (VT_INVN && P.inv_samples != 0.0) {                               // n is a power of two: x / n == x * (1 / n) exactly
+            mr = u2d((uint32_t)sr) * P.inv_samples; mg = u2d((uint32_t)sg) * P.inv_samples;
+            mb = u2d((uint32_t)sb) * P.inv_samples; ma = u2d((uint32_t)sa) * P.inv_samples;
+        } else {
+            const double dn = i2d(n);
+            mr = u2d((uint32_t)sr) / dn; mg = u2d((uint32_t)sg) / dn; mb = u2d((uint32_t)sb) / dn; ma = u2d((uint32_t)sa) / dn;
+        }
         if (P.mean) reinterpret_cast<float4 *>(P.mean)[i] = make_float4((float)mr, (float)mg, (float)mb, (float)ma);
         if (P.rgba8 || P.frame_target) {
             uchar4 q;                                                        // truncation, like a C cast
