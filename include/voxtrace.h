@@ -73,7 +73,8 @@ int vt_set_camera(vt_ctx *ctx, const double pos[3], const double rot_xyzw[4], do
 
 /* ---- world: what Camera.chunk_set / chunk_get expose (init.py:21-33) ------------------------------- */
 /* Declares the cell box covered by the camera's chunk dictionary: origin (world cell of the minimum corner)
- * and dims (cells), both multiples of chunk_size.  Drops any previous world.  Needs vt_set_settings first. */
+ * and dims (cells), both multiples of chunk_size.  Drops any previous world (its brick-pool memory is kept for the next
+ * one and released by vt_destroy; the tables are reused when the box has the same shape).  Needs vt_set_settings first. */
 int vt_set_world(vt_ctx *ctx, const int32_t origin[3], const int32_t dims[3]);
 /* Per-chunk-slot byte, [dims0/cs][dims1/cs][dims2/cs] (z fastest): 0 = no frame for that chunk (absent or
  * culled, init.py:447-452), else Frame.resolution of the frame the camera holds (init.py:448-450). */
