@@ -69,6 +69,7 @@ class GpuCamera:
         self.chunks = {}
         self.background = background_function if background is _UNSET else background
         # device-side state
+        self._known_posts = set()      # every chunk position chunk_set was ever called with (frame or None)
         self._mirror = None
         self._uploaded = {}            # post -> (frame object, resolution) last flattened
         self._mat_ids = {}             # id(Material) -> (index, Material)
@@ -79,6 +80,7 @@ class GpuCamera:
         self._counters = torch.zeros(16, dtype=torch.int64, device=self.device)
         self._pix_cache = {}
         self._static_materials = None
+        self._mats_sent = None
         self._world_shape = None
         self._world_origin = None
 
@@ -114,6 +116,13 @@ class GpuCamera:
         key = (self.settings.key(), self.background is not None)
         if key != self._settings_key:
             st = self.settings.to_struct(background=self.background is not None)
+            if self._mirror is not None and self._mirror.cs != int(self.settings.chunk_size):
+                # data.settings.chunk_size was edited in place: the chunk dictionary is keyed by the old size, so the
+                # device world is dropped and rebuilt from whatever chunk_set holds now (vt_set_settings refuses a
+                # chunk_size change while a world is loaded)
+                self._check(self._lib.vt_clear_world(self._ctx))
+                self._mirror, self._uploaded, self._visited = None, {}, None
+                self._known_posts = set(self.chunks)
             self._check(self._lib.vt_set_settings(self._ctx, C.byref(st)))
             self._settings_key = key
 
@@ -122,6 +131,9 @@ class GpuCamera:
         """init.py:21-25."""
         if self._dense_mode:
             raise VoxtraceError("chunk_set after set_world_dense: pick one world path per camera")
+        # Window.chunk_update calls this for EVERY chunk it knows, with None for the culled ones (init.py:447-452):
+        # the positions are remembered so that the visited-chunk grid covers them (see _sync_world)
+        self._known_posts.add(tuple(int(v) for v in post))
         if chunk:
             self.chunks[post] = chunk
         elif post in self.chunks:
@@ -150,6 +162,8 @@ class GpuCamera:
         return ent[0]
 
     def _push_materials(self):
+        """Material rows -> device.  Mods may mutate Material attributes in place (README.md:77), so the table is
+        rebuilt every frame, but it is sent only when a value changed."""
         if self._static_materials is not None:
             table = self._static_materials
         else:
@@ -158,31 +172,62 @@ class GpuCamera:
                 a = m.albedo
                 rgb = (a.r, a.g, a.b) if hasattr(a, "r") else tuple(a)
                 table[idx] = (rgb[0], rgb[1], rgb[2], m.roughness, m.absorption, m.ior, m.energy)
+        if self._mats_sent is not None and self._mats_sent.shape == table.shape and np.array_equal(self._mats_sent, table):
+            return
         n = table.shape[0] - 1
-        arr = (VtMaterial * (n + 1))()
-        for i in range(n + 1):
-            arr[i].albedo[:] = [float(v) for v in table[i, :3]]
-            arr[i].roughness, arr[i].absorption, arr[i].ior, arr[i].energy = (float(v) for v in table[i, 3:7])
-        self._check(self._lib.vt_set_materials(self._ctx, arr, n))
+        rows = np.zeros((n + 1, 8), np.float64)          # vt_material: albedo[3], roughness, absorption, ior, energy, reserved
+        rows[:, :7] = table
+        self._check(self._lib.vt_set_materials(self._ctx, rows.ctypes.data, n))
+        self._mats_sent = np.array(table, copy=True)
+
+    def _reach_box(self):
+        """Chunk-aligned box no ray of this camera can leave: a ray travels less than dist_min + life + one step per axis
+        (|vel| <= 1 per axis: primary rays are not longer than 1, lib.py:372-376, and a bounce normalises the largest
+        axis to 1, lib.py:310-314); life <= dist_max * detail with detail <= 1 + max(0, -lod_edge) (init.py:56, 133)."""
+        s = self.settings
+        cs = int(s.chunk_size)
+        reach = float(s.dist_max) * (1.0 + max(0.0, -float(s.lod_edge))) + cs + 2
+        p = np.array(_xyz(self.pos), np.float64)
+        lo = (np.floor((p - reach) / cs) * cs).astype(np.int64)
+        hi = (np.floor((p + reach) / cs) * cs).astype(np.int64) + cs
+        return lo, hi
 
     def _sync_world(self):
-        """Flatten chunks whose Frame changed since the last call and upload the bricks they touch."""
+        """Flatten chunks whose Frame changed since the last call and upload the bricks they touch.
+
+        The device box (brick table, chunk table, visited grid) spans every chunk position chunk_set was ever called
+        with.  With settings.culling on it also spans the camera's reach: the reference appends EVERY chunk position a
+        ray snaps into to ray.traversed, empty and culled ones included (init.py:67-73), and chunk_update tests
+        `post_chunk in traversed` against Window.chunks, not cam.chunks (init.py:447) -- on the first frame cam.chunks is
+        empty and the picture only ever appears because those positions are reported."""
         if self._dense_mode:
             return
-        cs = int(self.settings.chunk_size)
-        posts = [tuple(int(v) for v in p) for p in self.chunks]
-        if not posts:
-            posts = [(0, 0, 0)]
+        s = self.settings
+        cs = int(s.chunk_size)
         if self._mirror is None or self._mirror.cs != cs:
             self._mirror, self._uploaded = WorldMirror(cs), {}
-        lo, dims = self._mirror.box_for(posts)
+        posts = set(self._known_posts) | {tuple(int(v) for v in p) for p in self.chunks}
+        lo = hi = None
+        if posts:
+            lo, dims = self._mirror.box_for(posts)
+            hi = lo + dims
+        if bool(getattr(s, "culling", False)) or lo is None:
+            rlo, rhi = self._reach_box() if bool(getattr(s, "culling", False)) else (np.zeros(3, np.int64), np.full(3, cs, np.int64))
+            lo = rlo if lo is None else np.minimum(lo, rlo)
+            hi = rhi if hi is None else np.maximum(hi, rhi)
+        dims = hi - lo
         rebuilt = False
         if not self._mirror.covers(lo, dims):
-            if self._mirror.origin is not None:      # grow: keep the old box inside the new one
-                old_lo, old_hi = self._mirror.origin, self._mirror.origin + np.array(self._mirror.cells.shape)
-                hi = np.maximum(lo + dims, old_hi)
-                lo = np.minimum(lo, old_lo)
-                dims = hi - lo
+            if bool(getattr(s, "culling", False)):       # room to move before the next rebuild
+                lo, hi = lo - 4 * cs, hi + 4 * cs
+            if self._mirror.origin is not None:
+                # grow: keep the old box inside the new one, unless that makes it more than twice the size needed
+                # (a camera that walked far away from where it started)
+                old_lo, old_hi = self._mirror.origin, self._mirror.origin + self._mirror.dims
+                glo, ghi = np.minimum(lo, old_lo), np.maximum(hi, old_hi)
+                if np.all(ghi - glo <= 2 * (hi - lo)):
+                    lo, hi = glo, ghi
+            dims = hi - lo
             self._mirror.reset(lo, dims)
             self._uploaded = {}
             o = (C.c_int32 * 3)(*[int(v) for v in lo])
@@ -258,7 +303,7 @@ class GpuCamera:
             shape = self._world_shape
         else:
             self._sync_world()
-            shape = tuple(int(v) for v in self._mirror.cells.shape)
+            shape = tuple(int(v) for v in self._mirror.dims)
         if shape is None:
             raise VoxtraceError("download_dense: no world")
         out = torch.empty(shape, dtype=torch.uint8, device=self.device)
@@ -272,7 +317,7 @@ class GpuCamera:
         cs = int(self.settings.chunk_size)
         if not self._dense_mode:
             self._sync_world()
-        world = self._world_shape if self._dense_mode else tuple(int(v) for v in self._mirror.cells.shape)
+        world = self._world_shape if self._dense_mode else tuple(int(v) for v in self._mirror.dims)
         shape = tuple(v // cs for v in world)
         out = np.empty(shape, np.uint8)
         self._check(self._lib.vt_chunk_presence(self._ctx, out.ctypes.data, out.size))
@@ -357,8 +402,9 @@ class GpuCamera:
         return bits.reshape(shape)
 
     def traversed(self, visited_bits):
-        """Chunk-origin tuples of the slots a frame touched -- what tile() returns as ``traversed``
-        (init.py:143, 150); restricted to the chunk grid the camera holds, which is all init.py:447 looks up."""
+        """Chunk-origin tuples of the slots a frame touched -- what tile() returns as ``traversed`` (init.py:143, 150).
+        The grid spans every chunk position chunk_update ever named and, with culling on, the camera's reach (see
+        _sync_world), i.e. every position init.py:447 can look up."""
         origin, _ = self._chunk_grid()
         cs = int(self.settings.chunk_size)
         idx = np.argwhere(self.visited_slots(visited_bits))

@@ -60,11 +60,30 @@ C5_KEYS = ["000000", "3f3f3f", "7f7f7f", "bfbfbf", "ffffff", "ffff00", "00ffff",
 C5_MATERIALS = np.array([(0,) * 7, METAL, STONE_DARK, STONE_GRAY, STONE_LIGHT, MARBLE, LIGHT, GLASS, MIST], np.float64)
 
 
+def goxel_model_grid(size=(512, 256, 512), shapes=80, seed=5678):
+    """The C5 model as the dense engine-space grid [sx, sy, sz] of colour indices 1..8 (0 = empty): what loading the file
+    written from ``goxel_model`` gives back (every listed voxel lands inside the sprite box)."""
+    return _goxel_grid(size, shapes, np.random.default_rng(seed))
+
+
 def goxel_model(size=(512, 256, 512), shapes=80, seed=5678, target_voxels=None):
     """C5: shell-filled union of random boxes and spheres (engine axes: size = x, y, z), eight colours.
     Returns (xyz_file int32 [n, 3] in Goxel FILE coordinates, colour strings [n]) -- what a Goxel export of the model
     would list; engine position = (size.x - x_file, z_file, y_file) (data.py:285)."""
     rng = np.random.default_rng(seed)
+    sx = size[0]
+    grid = _goxel_grid(size, shapes, rng)
+    ex, ey, ez = np.nonzero(grid)
+    if target_voxels is not None and len(ex) > target_voxels:
+        keep = np.sort(rng.choice(len(ex), target_voxels, replace=False))
+        ex, ey, ez = ex[keep], ey[keep], ez[keep]
+    col = grid[ex, ey, ez]
+    # engine (x, y, z) -> file (size.x - x, z, y)
+    xyz_file = np.stack([sx - ex, ez, ey], axis=1).astype(np.int32)
+    return xyz_file, np.asarray(C5_KEYS)[col - 1]
+
+
+def _goxel_grid(size, shapes, rng):
     sx, sy, sz = size
     grid = np.zeros((sx, sy, sz), np.uint8)
     for k in range(shapes):
@@ -84,11 +103,28 @@ def goxel_model(size=(512, 256, 512), shapes=80, seed=5678, target_voxels=None):
             d = np.sqrt(((gx - c[0]) / max(1, r3[0])) ** 2 + ((gy - c[1]) / max(1, r3[1])) ** 2 + ((gz - c[2]) / max(1, r3[2])) ** 2)
             shell = (d <= 1.0) & (d >= 1.0 - thick / max(1, min(r3)))
         sub[shell] = col
-    ex, ey, ez = np.nonzero(grid)
-    if target_voxels is not None and len(ex) > target_voxels:
-        keep = np.sort(rng.choice(len(ex), target_voxels, replace=False))
-        ex, ey, ez = ex[keep], ey[keep], ez[keep]
-    col = grid[ex, ey, ez]
-    # engine (x, y, z) -> file (size.x - x, z, y)
-    xyz_file = np.stack([sx - ex, ez, ey], axis=1).astype(np.int32)
-    return xyz_file, np.asarray(C5_KEYS)[col - 1]
+    return grid
+
+
+# ---- the named configurations (BASELINE.json configs[3], configs[4]), shared by tests and bench.py
+C4_SETTINGS = dict(width=3840, height=2160, samples=16, static=True, shutter=0.25, falloff=0.25, dof=0.5, dist_min=0,
+                   dist_max=768, max_light=1, max_bounces=4, lod_bounces=0.5, lod_samples=0, lod_random=0.25,
+                   lod_edge=0, chunk_size=16, chunk_lod=2, fov=90, culling=False)
+C5_SETTINGS = dict(width=1920, height=1080, samples=8, static=True, shutter=0.25, falloff=0.25, dof=0.5, dist_min=0,
+                   dist_max=384, max_light=1, max_bounces=4, lod_bounces=0.5, lod_samples=0, lod_random=0.25,
+                   lod_edge=0, chunk_size=16, chunk_lod=2, fov=90, culling=True)
+C4_POS, C4_YAWS, C4_PITCH = (0.0, 300.0, 0.0), (0.0, 90.0, 135.0, 270.0), 30.0      # camera 30 degrees down, four yaw angles
+C5_SIZE, C5_POS, C5_EULER = (512, 256, 512), (-300.0, 40.0, -300.0), (0.0, 45.0, 10.0)
+
+
+def c4_workload(n=512):
+    """C4: (origin, cells, materials, chunk_res, poses) -- the per-chunk LOD table depends on the camera position only,
+    which the four poses share."""
+    from .mathutil import euler_to_quaternion
+    from .world import chunk_presence, lod_table
+    sd = C4_SETTINGS
+    origin, cells, mats = terrain_world(n)
+    present = chunk_presence(cells, sd["chunk_size"])
+    res = lod_table(origin, present, C4_POS, sd["chunk_size"], sd["chunk_lod"], sd["dist_max"])
+    poses = [dict(pos=C4_POS, rot=euler_to_quaternion(0.0, yaw, C4_PITCH)) for yaw in C4_YAWS]
+    return origin, cells, mats, res, poses

@@ -47,12 +47,15 @@ def flatten_frame(frame, post, chunk_size, mat_id):
 
 
 class WorldMirror:
-    """Dense host mirror of the device grid; turns dirty chunks into the list of bricks to upload."""
+    """Host mirror of the device grid, kept per chunk (the world box may be much larger than the chunks that hold
+    voxels: with culling on it spans the camera's reach, see GpuCamera._sync_world); turns dirty chunks into the list
+    of bricks to upload."""
 
     def __init__(self, chunk_size):
         self.cs = int(chunk_size)
         self.origin = None          # np.int64[3]
-        self.cells = None           # [nx, ny, nz] u8
+        self.dims = None            # np.int64[3], cells per axis
+        self.chunk_cells = {}       # slot (cx, cy, cz) -> [cs, cs, cs] u8 (only chunks that hold a voxel)
         self.chunk_res = None       # [ncx, ncy, ncz] u8
 
     def box_for(self, posts):
@@ -64,11 +67,12 @@ class WorldMirror:
     def covers(self, lo, dims):
         if self.origin is None:
             return False
-        return bool(np.all(lo >= self.origin) and np.all(lo + dims <= self.origin + np.array(self.cells.shape)))
+        return bool(np.all(lo >= self.origin) and np.all(lo + dims <= self.origin + self.dims))
 
     def reset(self, lo, dims):
         self.origin = np.asarray(lo, dtype=np.int64)
-        self.cells = np.zeros(tuple(int(d) for d in dims), np.uint8)
+        self.dims = np.asarray(dims, dtype=np.int64)
+        self.chunk_cells = {}
         self.chunk_res = np.zeros(tuple(int(d) // self.cs for d in dims), np.uint8)
 
     def slot(self, post):
@@ -76,31 +80,55 @@ class WorldMirror:
 
     def write_chunk(self, post, cells, res):
         """Stores one chunk; returns the set of brick coordinates (relative to origin) that changed."""
-        rel = np.asarray(post, dtype=np.int64) - self.origin
-        x, y, z = (int(v) for v in rel)
+        slot = self.slot(post)
+        x, y, z = (int(v) * self.cs for v in slot)
         cs = self.cs
-        view = self.cells[x:x + cs, y:y + cs, z:z + cs]
-        self.chunk_res[self.slot(post)] = res
+        self.chunk_res[slot] = res
+        old = self.chunk_cells.get(slot)
+        if cells is not None and not cells.any():
+            cells = None
         if cells is None:
-            cells = np.zeros_like(view)
-        if np.array_equal(view, cells):
-            return set()
-        view[...] = cells
+            if old is None:
+                return set()
+            del self.chunk_cells[slot]
+        else:
+            if old is not None and np.array_equal(old, cells):
+                return set()
+            self.chunk_cells[slot] = np.ascontiguousarray(cells, dtype=np.uint8).copy()
         bx = range(x // BRICK, (x + cs - 1) // BRICK + 1)
         by = range(y // BRICK, (y + cs - 1) // BRICK + 1)
         bz = range(z // BRICK, (z + cs - 1) // BRICK + 1)
         return {(i, j, k) for i in bx for j in by for k in bz}
 
     def gather_bricks(self, coords):
-        """coords: iterable of brick coords -> (int32[m,3], u8[m,512]) in the device's brick layout."""
+        """coords: iterable of brick coords -> (int32[m,3], u8[m,512]) in the device's brick layout.  A brick may
+        straddle chunks when chunk_size is not a multiple of 8."""
         coords = sorted(coords)
-        m = len(coords)
+        m, cs = len(coords), self.cs
         out = np.zeros((m, BRICK, BRICK, BRICK), np.uint8)
-        nx, ny, nz = self.cells.shape
-        for i, (bx, by, bz) in enumerate(coords):
-            blk = self.cells[bx * 8:min(bx * 8 + 8, nx), by * 8:min(by * 8 + 8, ny), bz * 8:min(bz * 8 + 8, nz)]
-            out[i, :blk.shape[0], :blk.shape[1], :blk.shape[2]] = blk
+        for i, b in enumerate(coords):
+            lo = [b[a] * BRICK for a in range(3)]
+            hi = [min(lo[a] + BRICK, int(self.dims[a])) for a in range(3)]
+            for cx in range(lo[0] // cs, (hi[0] - 1) // cs + 1):
+                for cy in range(lo[1] // cs, (hi[1] - 1) // cs + 1):
+                    for cz in range(lo[2] // cs, (hi[2] - 1) // cs + 1):
+                        blk = self.chunk_cells.get((cx, cy, cz))
+                        if blk is None:
+                            continue
+                        c0 = (cx * cs, cy * cs, cz * cs)
+                        s0 = [max(lo[a], c0[a]) for a in range(3)]
+                        s1 = [min(hi[a], c0[a] + cs) for a in range(3)]
+                        out[i, s0[0] - lo[0]:s1[0] - lo[0], s0[1] - lo[1]:s1[1] - lo[1], s0[2] - lo[2]:s1[2] - lo[2]] = \
+                            blk[s0[0] - c0[0]:s1[0] - c0[0], s0[1] - c0[1]:s1[1] - c0[1], s0[2] - c0[2]:s1[2] - c0[2]]
         return np.asarray(coords, dtype=np.int32).reshape(m, 3), out.reshape(m, 512)
+
+    def dense(self):
+        """The whole box as one [nx, ny, nz] u8 array (tests)."""
+        out = np.zeros(tuple(int(d) for d in self.dims), np.uint8)
+        cs = self.cs
+        for (cx, cy, cz), blk in self.chunk_cells.items():
+            out[cx * cs:(cx + 1) * cs, cy * cs:(cy + 1) * cs, cz * cs:(cz + 1) * cs] = blk
+        return out
 
 
 def lod_table(origin, present, cam_pos, chunk_size, chunk_lod, dist_max, visible=None):

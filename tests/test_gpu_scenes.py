@@ -105,12 +105,7 @@ def test_builder_object_order_and_offsets():
 
 
 # ------------------------------------------------------------------------------------------- C4 / C5 at full size
-C4_SETTINGS = dict(width=3840, height=2160, samples=16, static=True, shutter=0.25, falloff=0.25, dof=0.5, dist_min=0,
-                   dist_max=768, max_light=1, max_bounces=4, lod_bounces=0.5, lod_samples=0, lod_random=0.25,
-                   lod_edge=0, chunk_size=16, chunk_lod=2, fov=90, culling=False)
-C5_SETTINGS = dict(width=1920, height=1080, samples=8, static=True, shutter=0.25, falloff=0.25, dof=0.5, dist_min=0,
-                   dist_max=384, max_light=1, max_bounces=4, lod_bounces=0.5, lod_samples=0, lod_random=0.25,
-                   lod_edge=0, chunk_size=16, chunk_lod=2, fov=90, culling=True)
+from python_raytracer_b200.scenes import C4_SETTINGS, C5_SETTINGS  # noqa: E402
 
 
 def _sample_pixels(w, h, n, seed):
