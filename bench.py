@@ -218,8 +218,11 @@ def run_ours(args, rank, world, local_rank):
     t_total = sum(a.elapsed_time(c) for a, _, c in ev)          # ms, render + gather
     t_kernel = sum(a.elapsed_time(b) for a, b, _ in ev)         # ms, this rank's render kernel only
     tt = torch.tensor([t_total, t_kernel], dtype=torch.float64, device=dev)
+    per_rank = [tt.clone() for _ in range(world)]
     if world > 1:
+        dist.all_gather(per_rank, tt)
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    rank_kernel_ms = sorted(float(t[1]) / args.steps for t in per_rank)
     t_total, t_kernel = float(tt[0]), float(tt[1])
     ms_step = t_total / args.steps
     value = rays_frame / (ms_step * 1e-3)
@@ -294,6 +297,8 @@ def run_ours(args, rank, world, local_rank):
             "ms_per_step": ms_step, "ms_median": ms_median, "ms_p95": ms_p95, "frames_per_sec": 1000.0 / ms_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(world, use_peer),
             "clocks": clocks, "gpu_launches": int(launches),
+            "rank_kernel_ms": {"min": rank_kernel_ms[0], "median": rank_kernel_ms[len(rank_kernel_ms) // 2], "max": rank_kernel_ms[-1],
+                               "all": [round(v, 5) for v in rank_kernel_ms]},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": 1000.0 * float(te[0]) / args.steps,
                     "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h},
             "roofline": roofline}

@@ -24,6 +24,7 @@ extern "C" {
 #define VT_BRICK 8                 /* bricks are 8x8x8 cells = 512 bytes */
 #define VT_MAX_MATERIALS 255       /* material id 0 is "empty" */
 #define VT_RAY_RECORD 16           /* doubles per ray record (see vt_render) */
+#define VT_TRACE_RECORD 20         /* doubles per record of vt_trace_rays */
 
 typedef struct vt_ctx vt_ctx;
 
@@ -59,6 +60,10 @@ int vt_abi_version(void);
 /* Build variant of the loaded library: bit 0 = bounds-checked kernels (-DVT_CHECKED=1, tests/check_bounds.sh),
  * bit 1 = phase-trip instrumentation (-DVT_TRIPS=1, tools/kbench.py).  0 for the product build. */
 int vt_build_flags(void);
+/* Scheduling knobs of the render kernel for A/B measurements (tools/kbench.py): "runs" 0/1 brick-local loops, "powtab"
+ * 0/1 memoised falloff power, "refill" 1..32 idle lanes that trigger a refill, "group" 1..32 lanes per pixel of a packet,
+ * "debug" 0/1.  None changes a result and the product never calls it (nothing is read from the environment). */
+int vt_set_tuning(vt_ctx *ctx, const char *key, int value);
 /* Use an existing CUDA stream (cudaStream_t, e.g. torch's current stream) instead of the context's own. */
 int vt_set_stream(vt_ctx *ctx, void *cuda_stream);
 int vt_sync(vt_ctx *ctx);
@@ -76,6 +81,9 @@ int vt_set_camera(vt_ctx *ctx, const double pos[3], const double rot_xyzw[4], do
  * and dims (cells), both multiples of chunk_size.  Drops any previous world (its brick-pool memory is kept for the next
  * one and released by vt_destroy; the tables are reused when the box has the same shape).  Needs vt_set_settings first. */
 int vt_set_world(vt_ctx *ctx, const int32_t origin[3], const int32_t dims[3]);
+/* Drops the world and releases its memory; afterwards vt_set_settings accepts another chunk_size (an engine that edits
+ * data.settings.chunk_size in place, data.py:41). */
+int vt_clear_world(vt_ctx *ctx);
 /* Per-chunk-slot byte, [dims0/cs][dims1/cs][dims2/cs] (z fastest): 0 = no frame for that chunk (absent or
  * culled, init.py:447-452), else Frame.resolution of the frame the camera holds (init.py:448-450). */
 int vt_set_chunk_table(vt_ctx *ctx, const uint8_t *host_res, int64_t n_slots);
@@ -155,11 +163,23 @@ typedef struct {
  * frame_seed perturbs the Philox streams when settings.static is 0; ignored when it is 1. */
 int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
               uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed);
+/* Camera.trace(dir_x, dir_y, detail) (init.py:37-121) for n caller-given rays: dev_dirs [n][3] f64 = dir_x, dir_y, detail
+ * (detail scales the ray's life as given, init.py:56; no lod_random draw -- that happens in tile, init.py:139).  Ray i
+ * draws its dof / roughness jitter from the Philox stream keyed i (n <= 65535 * width).  dev_sincos (nullable, used
+ * when dof == 0): [n][4] f64 sin, cos of the half yaw angle -lens_x / 2 and sin, cos of the half pitch angle lens_y / 2
+ * in radians (init.py:41-43, lib.py:322-332) computed by the caller with the libm the reference's interpreter uses;
+ * without it the device evaluates them (<= 1 ulp).  dev_records [n][VT_TRACE_RECORD] f64 = the returned ray: r, g, b,
+ * energy, bounces, step, hits, first-hit x, y, z, first-hit flag, first-hit step, vel x, y, z, life, pos x, y, z, 0.
+ * dev_visited / dev_counters as in vt_render (ray.traversed of all rays, OR-ed). */
+int vt_trace_rays(vt_ctx *ctx, const double *dev_dirs, const double *dev_sincos, int64_t n, double *dev_records,
+                  uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed);
+
 /* ---- multi-GPU frame assembly over peer memory (replaces the pool's result pipes, init.py:185-190, 205) -------
  * One process per GPU.  Rank 0 owns the full frame(s) and an array of arrival flags in memory from vt_shared_alloc;
  * the other ranks open them with CUDA IPC and render with a FRAME TARGET: every finished pixel is stored at
  * frame[(y * width + x) * 4] -- a store over NVLink when the frame is a peer's -- and when a rank's launch is
- * complete its last warp publishes `arrive_value` in its arrival flag (system-scope fence first).  Rank 0 queues
+ * complete its last warp publishes `arrive_value` in its arrival flag (system-scope fence first; a rank whose region
+ * is empty publishes it too).  Rank 0 queues
  * vt_stream_wait_flags on its stream instead of a collective.  Flag values only grow (frame numbers).
  * vt_stream_signal_flags is the reverse direction (rank 0 hands a frame buffer back to the renderers). */
 int vt_shared_alloc(vt_ctx *ctx, int64_t bytes, void **out_dev_ptr);     /* zero-filled, plain cudaMalloc */
@@ -169,6 +189,11 @@ int vt_ipc_open(vt_ctx *ctx, const uint8_t handle[64], void **out_dev_ptr);
 int vt_ipc_close(vt_ctx *ctx, void *dev_ptr);
 /* dev_frame NULL switches the target off.  Rectangle regions only; dev_rgba8 of vt_render may then be NULL. */
 int vt_set_frame_target(vt_ctx *ctx, uint8_t *dev_frame, uint32_t *dev_arrive_flag, uint32_t arrive_value);
+/* Multi-GPU culling -- the union of the workers' traversed lists (init.py:189, 393).  With a frame target set, the last
+ * warp of every vt_render launch that is given dev_visited ORs the launch's visited words into dev_peer_mask (n_words
+ * u32 in a peer's memory, e.g. rank 0's, opened with vt_ipc_open) before it raises the arrival flag, so whoever has
+ * seen all arrival flags holds the union.  NULL switches it off. */
+int vt_set_visited_peer(vt_ctx *ctx, uint32_t *dev_peer_mask, int64_t n_words);
 /* Stream-ordered: continue once flags[0..n) have all reached `value` (n <= 32).  A wait longer than timeout_s
  * (default 2 s) gives up and records 1 + flag index for vt_wait_status instead of hanging the GPU. */
 int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t value, double timeout_s);

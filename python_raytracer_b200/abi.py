@@ -10,13 +10,15 @@ SETTINGS_INT = ("width", "height", "samples", "static_noise", "chunk_size", "chu
 SETTINGS_F64 = ("shutter", "falloff", "dof", "dist_min", "dist_max", "max_light", "max_bounces",
                 "lod_bounces", "lod_samples", "lod_random", "lod_edge", "proportions")
 RAY_RECORD = 16
+TRACE_RECORD = 20
 
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
            "vt_set_settings", "vt_set_materials", "vt_set_camera", "vt_set_world", "vt_set_chunk_table",
            "vt_upload_bricks", "vt_upload_dense", "vt_chunk_presence", "vt_download_dense", "vt_world_stats", "vt_render", "vt_region_pixels",
            "vt_launch_count", "vt_build_flags", "vt_build_world", "vt_update_region", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
-           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw")
+           "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw",
+           "vt_set_tuning", "vt_clear_world", "vt_trace_rays", "vt_set_visited_peer")
 
 
 class VtSettings(C.Structure):
@@ -103,6 +105,10 @@ def load(path: str | None = None):
         "vt_stream_signal_flags_on": (C.c_int, [vp, vp, C.POINTER(vp), i32, C.c_uint32]),
         "vt_wait_status": (C.c_int, [vp, C.POINTER(C.c_int)]),
         "vt_copy_to_host": (C.c_int, [vp, vp, vp, i64]),
+        "vt_set_tuning": (C.c_int, [vp, C.c_char_p, i32]),
+        "vt_clear_world": (C.c_int, [vp]),
+        "vt_trace_rays": (C.c_int, [vp, vp, vp, i64, vp, vp, vp, u64]),
+        "vt_set_visited_peer": (C.c_int, [vp, vp, i64]),
         "vt_fx_compose": (C.c_int, [vp, vp, vp, i64]),
         "vt_fx_draw": (C.c_int, [vp, C.POINTER(VtFx), vp, vp, C.POINTER(C.c_int32)]),
     }

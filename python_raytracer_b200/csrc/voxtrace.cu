@@ -84,7 +84,10 @@ struct vt_ctx {
     int sm_count = 0;
     int max_res = 0;                                                // largest Frame.resolution in the chunk table
     int brick_runs = 1;                                             // VT_RUNS=0 disables empty-brick runs (A/B)
-    int refill_min = 32;                                            // VT_REFILL overrides
+    int refill_min = 32;                                            // vt_set_tuning("refill")
+    int group_max = 1;                                              // vt_set_tuning("group"): lanes per pixel of a packet
+    int debug = 0;
+    uint32_t *visited_peer = nullptr; int visited_words = 0;        // vt_set_visited_peer
     // multi-GPU frame target (vt_set_frame_target) and the status word of the wait kernel
     uint8_t *frame_target = nullptr; unsigned int *arrive_flag = nullptr; unsigned int arrive_value = 0;
     int *d_wait_status = nullptr; int clock_khz = 0;
@@ -140,16 +143,27 @@ extern "C" int vt_create(int device, vt_ctx **out) {
         delete ctx;
         return 2;
     }
-    if (const char *k = getenv("VT_RUNS")) ctx->brick_runs = atoi(k) != 0;
-    if (const char *k = getenv("VT_POWTAB")) ctx->pow_tab_on = atoi(k) != 0;
     if ((e = cudaMalloc(&ctx->d_pow_tab, VT_POW_SLOTS * 2 * sizeof(unsigned long long))) != cudaSuccess ||
         (e = cudaMemset(ctx->d_pow_tab, 0, VT_POW_SLOTS * 2 * sizeof(unsigned long long))) != cudaSuccess) {
         g_create_err = std::string("vt_create: ") + cudaGetErrorString(e);
         delete ctx;
         return 2;
     }
-    if (const char *k = getenv("VT_REFILL")) { int v = atoi(k); if (v >= 1 && v <= 32) ctx->refill_min = v; }
     *out = ctx;
+    return 0;
+}
+
+// Scheduling knobs of the render kernel for A/B measurements (tools/kbench.py).  None of them changes a result; the
+// product never calls this (the defaults are the measured optimum).
+extern "C" int vt_set_tuning(vt_ctx *ctx, const char *key, int value) {
+    if (!ctx || !key) return 1;
+    const std::string k(key);
+    if (k == "runs") ctx->brick_runs = value != 0;                  // 0: no brick-local loops
+    else if (k == "powtab") ctx->pow_tab_on = value != 0;           // 0: no memoised falloff power
+    else if (k == "refill") { if (value < 1 || value > 32) return fail(ctx, "vt_set_tuning: refill must be 1..32"); ctx->refill_min = value; }
+    else if (k == "group") { if (value < 1 || value > 32) return fail(ctx, "vt_set_tuning: group must be 1..32"); ctx->group_max = value; }
+    else if (k == "debug") ctx->debug = value;
+    else return fail(ctx, "vt_set_tuning: unknown key");
     return 0;
 }
 
@@ -287,6 +301,17 @@ extern "C" int vt_set_world(vt_ctx *ctx, const int32_t origin[3], const int32_t 
     ctx->pool_used = 0; ctx->free_slots.clear(); ctx->mirror_stale = false;
     ctx->max_res = 0; ctx->world_cs = cs;
     ctx->have_world = true;
+    return 0;
+}
+
+// Drops the world (tables and brick pool released): afterwards vt_set_settings accepts another chunk_size.
+extern "C" int vt_clear_world(vt_ctx *ctx) {
+    if (!ctx) return 1;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    free_world(ctx);
+    for (int a = 0; a < 3; a++) { ctx->dims[a] = 0; ctx->nb[a] = 0; ctx->nc[a] = 0; }
+    ctx->world_cs = 0; ctx->max_res = 0;
     return 0;
 }
 
@@ -649,6 +674,14 @@ extern "C" int vt_set_frame_target(vt_ctx *ctx, uint8_t *dev_frame, uint32_t *de
     ctx->frame_target = dev_frame; ctx->arrive_flag = dev_frame ? dev_arrive_flag : nullptr; ctx->arrive_value = arrive_value;
     return 0;
 }
+// Multi-GPU culling: with a frame target set, the last warp of every vt_render launch that has dev_visited ORs the
+// launch's visited words into dev_peer_mask (n_words u32, typically in rank 0's memory, opened with vt_ipc_open) before
+// it raises the arrival flag -- the union of the workers' traversed lists (init.py:189, 393).  NULL switches it off.
+extern "C" int vt_set_visited_peer(vt_ctx *ctx, uint32_t *dev_peer_mask, int64_t n_words) {
+    if (!ctx || n_words < 0 || n_words > (1LL << 30)) return 1;
+    ctx->visited_peer = dev_peer_mask; ctx->visited_words = dev_peer_mask ? (int)n_words : 0;
+    return 0;
+}
 extern "C" int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t value, double timeout_s) {
     if (!ctx || !dev_flags || n < 1 || n > 32) return 1;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
@@ -851,7 +884,7 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
     if (ctx->persist_blocks[which] == 0) {
         int nb = 0;
         VT_CHECK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&nb, fn, 128, 0));
-        if (getenv("VT_DEBUG")) fprintf(stderr, "voxtrace: persistent kernel %d: %d blocks/SM\n", which, nb);
+        if (ctx->debug) fprintf(stderr, "voxtrace: persistent kernel %d: %d blocks/SM\n", which, nb);
         ctx->persist_blocks[which] = nb > 0 ? nb : 1;
     }
     long long want = (long long)((P.total_rays + 127) / 128);             // one ray slot per thread at least once
@@ -877,8 +910,10 @@ static int launch_persistent(vt_ctx *ctx, DevParams &P, bool rec, bool count) {
     return 0;
 }
 
-extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
-                         uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed) {
+struct TraceArgs { const double *dirs; const double *sincos; double *records; long long n; };
+
+static int render_impl(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
+                       uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed, const TraceArgs *trace) {
     if (!ctx || !region) return 1;
     if (!ctx->have_settings) return fail(ctx, "vt_render: no settings (vt_set_settings)");
     if (!ctx->have_world) return fail(ctx, "vt_render: no world (vt_set_world)");
@@ -901,11 +936,15 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
     P.cam.lens = ctx->cam_lens;
     if (int rc = update_dir_tables(ctx)) return rc;
     P.cam.dir_x = ctx->d_dir_x; P.cam.dir_y = ctx->d_dir_y;
-    if (s.dof == 0.0) {
+    if (s.dof == 0.0 && !trace) {
         if (int rc = update_lens_tables(ctx)) return rc;
         P.cam.col_sc = ctx->d_col_sc; P.cam.row_sc = ctx->d_row_sc;
     }
-    if (region->dev_pixels) {
+    if (trace) {
+        // ray i draws from the Philox stream keyed i = y * width + x with x, y < 65536
+        if (trace->n < 0 || trace->n > 65535LL * s.width) return fail(ctx, "vt_trace_rays: too many rays for one call");
+        P.dirs = trace->dirs; P.dir_sc = trace->sincos; P.trace_out = trace->records; P.n_pixels = trace->n;
+    } else if (region->dev_pixels) {
         if (region->n_pixels < 0) return fail(ctx, "vt_render: negative n_pixels");
         P.pixels = region->dev_pixels; P.n_pixels = region->n_pixels;
     } else {
@@ -921,10 +960,29 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
         P.band_rows = band_rows;
         P.n_pixels = (long long)band_rows * (region->x1 - region->x0);
     }
-    if (P.n_pixels == 0) return 0;
-    P.frame_target = ctx->frame_target; P.arrive_flag = ctx->arrive_flag; P.arrive_value = ctx->arrive_value;
-    if (ctx->frame_target && region->dev_pixels)
+    if (ctx->frame_target && !trace && region->dev_pixels)
         return fail(ctx, "vt_render: a frame target needs a rectangle region");
+    if (P.n_pixels == 0) {
+        // nothing to render (a rank whose stripe set is empty, e.g. a 48-row canvas split eight ways): the arrival flag
+        // must still go up, the consumer waits for one flag per rank
+        if (ctx->frame_target && ctx->arrive_flag && !trace) {
+            FlagTargets tg;
+            memset(&tg, 0, sizeof tg);
+            tg.p[0] = ctx->arrive_flag;
+            signal_flags_kernel<<<1, 32, 0, ctx->stream>>>(tg, 1, ctx->arrive_value);
+            ctx->launches++;
+            VT_CHECK(ctx, cudaGetLastError());
+        }
+        return 0;
+    }
+    if (!trace) {
+        P.frame_target = ctx->frame_target; P.arrive_flag = ctx->arrive_flag; P.arrive_value = ctx->arrive_value;
+        if (ctx->frame_target && ctx->visited_peer && dev_visited) {
+            const long long words = ((long long)ctx->nc[0] * ctx->nc[1] * ctx->nc[2] + 31) / 32;
+            if (words != ctx->visited_words) return fail(ctx, "vt_render: the peer visited mask does not match the world's chunk grid");
+            P.visited_peer = ctx->visited_peer; P.visited_words = ctx->visited_words;
+        }
+    }
     P.rgba8 = dev_rgba8; P.mean = dev_mean; P.ray0 = dev_ray0; P.visited = dev_visited;
     P.counters = reinterpret_cast<unsigned long long *>(dev_counters);
     // A packet of 32 ray slots is one sample index of an 8 x 4 pixel tile; the other samples of those pixels are
@@ -932,23 +990,39 @@ extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba
     // and a pixel's accumulator is then touched by different warps at different times (VT_GROUP=n: up to n lanes per
     // pixel instead; measured 1.7 % slower at 4 spp, equal at 8 and 16 spp).
     int G = 1, gs = 0;
-    int gmax = 1;
-    if (const char *k = getenv("VT_GROUP")) { int v = atoi(k); if (v >= 1 && v <= 32) gmax = v; }
+    const int gmax = trace ? 1 : ctx->group_max;
     while (G < s.samples && G < gmax) { G <<= 1; gs++; }
     const int ppw = 32 / G;
     static const int TW[6] = {8, 4, 4, 2, 2, 1};      // tile width for 32,16,8,4,2,1 pixels per warp
     int tw = TW[gs], tws = 0;
     while ((1 << tws) < tw) tws++;
     P.group = G; P.group_shift = gs; P.tile_w = tw; P.tile_w_shift = tws; P.tile_h = ppw / tw;
-    if (P.pixels) P.n_warps = (P.n_pixels + ppw - 1) / ppw;
+    if (P.pixels || trace) P.n_warps = (P.n_pixels + ppw - 1) / ppw;
     else {
         P.tiles_x = (P.x1 - P.x0 + tw - 1) / tw;
         P.n_warps = (long long)P.tiles_x * ((P.band_rows + P.tile_h - 1) / P.tile_h);
     }
-    if (int rc = launch_persistent(ctx, P, dev_ray0 != nullptr, dev_counters != nullptr)) return rc;
+    if (int rc = launch_persistent(ctx, P, dev_ray0 != nullptr || trace, dev_counters != nullptr)) return rc;
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     return 0;
+}
+
+extern "C" int vt_render(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8, float *dev_mean, double *dev_ray0,
+                         uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed) {
+    return render_impl(ctx, region, dev_rgba8, dev_mean, dev_ray0, dev_visited, dev_counters, frame_seed, nullptr);
+}
+
+// Camera.trace (init.py:37-121) for a batch of caller-given rays.
+extern "C" int vt_trace_rays(vt_ctx *ctx, const double *dev_dirs, const double *dev_sincos, int64_t n, double *dev_records,
+                             uint32_t *dev_visited, uint64_t *dev_counters, uint64_t frame_seed) {
+    if (!ctx || n < 0 || (n > 0 && (!dev_dirs || !dev_records))) return 1;
+    if (n == 0) return 0;
+    vt_region r;
+    memset(&r, 0, sizeof r);
+    r.stripe_rows = 1; r.stripe_count = 1;
+    TraceArgs t = {dev_dirs, dev_sincos, dev_records, (long long)n};
+    return render_impl(ctx, &r, nullptr, nullptr, nullptr, dev_visited, dev_counters, frame_seed, &t);
 }
 
 // ---- post-FX (vt_postfx.cuh) ------------------------------------------------------------------------------

@@ -84,6 +84,13 @@ struct DevParams {
     uint8_t *frame_target;
     unsigned int *arrive_flag;
     unsigned int arrive_value;
+    // multi-GPU culling: the launch's last warp ORs this rank's visited words into a peer's mask before the flag goes up
+    uint32_t *visited_peer;
+    int visited_words;
+    // trace mode (vt_trace_rays, REC instantiations only): rays given as (dir_x, dir_y, detail) triples, not pixels
+    const double *dirs;             // [n][3]
+    const double *dir_sc;           // [n][4] sin, cos of the half yaw, sin, cos of the half pitch (host libm; dof == 0) or null
+    double *trace_out;              // [n][VT_TRACE_RECORD]
     // outputs
     uint8_t *rgba8;
     float *mean;

@@ -502,6 +502,14 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
         cg = pmin(255.0, rint_d(cg * L.energy));
         cb = pmin(255.0, rint_d(cb * L.energy));
     }
+    if (REC && P.trace_out) {                                                // Camera.trace's return value (init.py:121)
+        double *o = P.trace_out + (size_t)VT_TRACE_RECORD * L.out_i;
+        o[0] = cr; o[1] = cg; o[2] = cb; o[3] = L.energy; o[4] = L.bounces; o[5] = L.step;
+        o[6] = i2d(fh.hits); o[7] = i2d(fh.fx); o[8] = i2d(fh.fy); o[9] = i2d(fh.fz);
+        o[10] = i2d(fh.fflag); o[11] = fh.first_step; o[12] = L.vx; o[13] = L.vy; o[14] = L.vz; o[15] = L.life;
+        o[16] = L.px; o[17] = L.py; o[18] = L.pz; o[19] = 0.0;
+        return;
+    }
     double alpha = rint_d(pmin(1.0, L.energy + s.shutter) * 255.0);            // init.py:141
     const int x = (int)(L.xy & 0xffffu), y = (int)(L.xy >> 16);
     double dx_, dy_, det_;
@@ -577,7 +585,13 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
     const uint32_t pi = slot >> P.group_shift, sample = (slot & (uint32_t)(P.group - 1)) + (uint32_t)P.group * round;
     int x = 0, y = 0;
     bool pv;
-    if (P.pixels) {
+    const bool tracing = REC && P.dirs != nullptr;                           // vt_trace_rays: slot i is ray i
+    if (tracing) {
+        const long long i = (long long)tile * 32 + pi;
+        pv = i < P.n_pixels;
+        // the Philox key of ray i is i itself: y * width + x below
+        if (pv) { y = (int)(i / s.width); x = (int)(i - (long long)y * s.width); L.out_i = (uint32_t)i; }
+    } else if (P.pixels) {
         long long i = (long long)tile * (32 >> P.group_shift) + pi;
         pv = i < P.n_pixels;
         if (pv) { x = __ldg(P.pixels + 2 * i); y = __ldg(P.pixels + 2 * i + 1); L.out_i = (uint32_t)i; }
@@ -591,16 +605,24 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
     }
     if (!pv) return;
     double dir_x, dir_y, detail;
-    const int n = pixel_samples(P, x, y, dir_x, dir_y, detail);
+    int n = 1;
+    if (tracing) { dir_x = __ldg(P.dirs + 3 * (size_t)L.out_i); dir_y = __ldg(P.dirs + 3 * (size_t)L.out_i + 1); detail = __ldg(P.dirs + 3 * (size_t)L.out_i + 2); }
+    else n = pixel_samples(P, x, y, dir_x, dir_y, detail);
     if ((int)sample >= n) return;
     rays++;
     L.xy = (uint32_t)x | ((uint32_t)y << 16);
     L.st = ST_MARCH | (sample << 12);
     L.draw = 0; L.w2 = L.w3 = 0;
-    double u = lane_rng_next(P, L);                                          // drawn even when lod_random == 0 (init.py:139)
-    double ray_detail = detail / (1.0 + u2d(sample) * s.lod_samples) * (1.0 - s.lod_random * u);
+    double ray_detail = detail;                                              // trace() takes `detail` as given (init.py:56)
+    if (!tracing) {
+        double u = lane_rng_next(P, L);                                      // drawn even when lod_random == 0 (init.py:139)
+        ray_detail = detail / (1.0 + u2d(sample) * s.lod_samples) * (1.0 - s.lod_random * u);
+    }
     double sy, cy, sz, cz;
-    if (s.dof == 0.0 && P.cam.col_sc) {
+    if (tracing && s.dof == 0.0 && P.dir_sc) {
+        const double *sc = P.dir_sc + 4 * (size_t)L.out_i;
+        sy = __ldg(sc); cy = __ldg(sc + 1); sz = __ldg(sc + 2); cz = __ldg(sc + 3);
+    } else if (!tracing && s.dof == 0.0 && P.cam.col_sc) {
         sy = __ldg(P.cam.col_sc + 2 * x); cy = __ldg(P.cam.col_sc + 2 * x + 1);
         sz = __ldg(P.cam.row_sc + 2 * y); cz = __ldg(P.cam.row_sc + 2 * y + 1);
     } else {
@@ -714,10 +736,26 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
     // The last warp to leave resets the queue for the next launch and, with a frame target, publishes the arrival
     // flag: every thread's pixel stores are fenced at system scope first, so the peer that sees the flag sees the band.
     if (P.arrive_flag) { __threadfence_system(); __syncwarp(full); }
+    unsigned long long done = 0ull;
     if (lane == 0) {
         __threadfence();
-        unsigned long long done = atomicAdd(P.queue + 1, 1ull);
-        if (done == (unsigned long long)P.total_warps - 1ull) {
+        done = atomicAdd(P.queue + 1, 1ull);
+    }
+    done = __shfl_sync(full, done, 0);
+    if (done == (unsigned long long)P.total_warps - 1ull) {
+        // Multi-GPU culling (init.py:189, 393: the workers' traversed lists are merged every frame): this rank's visited
+        // words -- complete now, every other warp has fenced and left -- are OR-ed into the peer's mask over NVLink,
+        // and the arrival flag that publishes the pixels publishes them too.
+        if (P.visited_peer && P.visited) {
+            __threadfence();
+            for (int w = lane; w < P.visited_words; w += 32) {
+                const uint32_t v = __ldcg(P.visited + w);
+                if (v) atomicOr_system(P.visited_peer + w, v);
+            }
+            __threadfence_system();
+            __syncwarp(full);
+        }
+        if (lane == 0) {
             P.queue[0] = 0ull; P.queue[1] = 0ull;
             if (P.arrive_flag) { __threadfence_system(); atomicExch_system(P.arrive_flag, P.arrive_value); }
         }

@@ -1,8 +1,8 @@
 #!/usr/bin/env python
 """Kernel A/B timing on the bench workload (dev tool, not a test):  python tools/kbench.py [variant ...]
 
-A variant is a comma-separated list of ENV=VALUE pairs read by vt_create (VT_REFILL=n, VT_RUNS=0, VT_POWTAB=0) plus
-optionally LIB=<path to an alternative libvoxtrace.so>.  Prints ms/frame per camera pose.
+A variant is a comma-separated list of key=value pairs handed to vt_set_tuning (refill=n, runs=0, powtab=0, group=n) plus
+optionally LIB=<path to an alternative libvoxtrace.so> (tools/build_variants.py).  Prints ms/frame per camera pose.
 """
 import json
 import os
@@ -20,9 +20,6 @@ from python_raytracer_b200 import GpuCamera, Settings, abi
 def run_variant(spec, frames=8, settings=None, workload=None):
     env = dict(kv.split("=", 1) for kv in spec.split(",") if kv)
     lib = env.pop("LIB", None)
-    for k in [k for k in os.environ if k.startswith("VT_")]:
-        os.environ.pop(k, None)
-    os.environ.update(env)
     if lib:
         abi._lib = abi.load(os.path.join(ROOT, lib))
     else:
@@ -34,6 +31,8 @@ def run_variant(spec, frames=8, settings=None, workload=None):
     frames = int(os.environ.get("KB_FRAMES", frames))
     s = Settings.from_object(settings or bench.C3_SETTINGS)
     cam = GpuCamera(s, device=0, background_function=bench.BUILTIN_BG, background=bench.BUILTIN_BG)
+    for k, v in env.items():
+        cam._check(cam._lib.vt_set_tuning(cam._ctx, k.encode(), int(v)))
     cam.set_world_dense(origin, cells, poses[0]["chunk_res"], mats)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     out, ms = {}, []
