@@ -52,6 +52,9 @@ def lib():
         _lib.vto_render.restype = C.c_int
         _lib.vto_render.argtypes = [C.POINTER(Settings), C.POINTER(Camera), C.POINTER(Scene), C.c_void_p,
                                     C.c_int64, C.c_int, C.c_uint64, C.c_int] + [C.c_void_p] * 6
+        _lib.vto_trace_rays.restype = C.c_int
+        _lib.vto_trace_rays.argtypes = [C.POINTER(Settings), C.POINTER(Camera), C.POINTER(Scene), C.c_void_p, C.c_int64,
+                                        C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
         _lib.vto_py_floordiv.restype = C.c_double
         _lib.vto_py_floordiv.argtypes = [C.c_double, C.c_double]
         _lib.vto_py_mod.restype = C.c_double
@@ -140,3 +143,22 @@ def render(settings: dict, cam_pos, cam_rot, lens, world: World, pixels=None, rn
     if rc != 0:
         raise RuntimeError("vto_render failed: %d" % rc)
     return dict(mean=mean, rgba8=rgba8, nsamp=nsamp, ray0=ray0, visited=visited, counters=counters, pixels=pixels)
+
+
+def trace_rays(settings: dict, cam_pos, cam_rot, lens, world: World, dirs, rng=RNG_PHILOX, seed=0):
+    """Camera.trace (init.py:37-121) for ``dirs`` [n,3] = (dir_x, dir_y, detail).  Returns dict(records [n,20], visited,
+    counters); record columns: r g b energy bounces step hits fx fy fz fflag first_step vx vy vz life px py pz 0."""
+    L = lib()
+    s = make_settings(settings)
+    dirs = np.ascontiguousarray(dirs, dtype=np.float64).reshape(-1, 3)
+    n = dirs.shape[0]
+    cam = make_camera(cam_pos, cam_rot, lens)
+    sc = world.struct()
+    rec = np.zeros((n, 20), np.float64)
+    visited = np.zeros(world.chunk_res.shape, np.uint8)
+    counters = np.zeros(8, np.uint64)
+    rc = L.vto_trace_rays(C.byref(s), C.byref(cam), C.byref(sc), dirs.ctypes.data, n, int(rng), int(seed), rec.ctypes.data,
+                          visited.ctypes.data, counters.ctypes.data)
+    if rc != 0:
+        raise RuntimeError("vto_trace_rays failed: %d" % rc)
+    return dict(records=rec, visited=visited, counters=counters)

@@ -416,3 +416,38 @@ int vto_render(const vto_settings *s, const vto_camera *cam, const vto_scene *sc
     free(jobs); free(tids);
     return 0;
 }
+
+/* Camera.trace (init.py:37-121) for caller-given (dir_x, dir_y, detail) triples, one after the other.  In Philox mode
+ * ray i draws from the stream keyed i (sample 0, draw 0 first: trace() itself draws dof x, dof y, then the hits'
+ * jitter -- the lod_random draw belongs to tile, init.py:139); in MT19937 mode the generator is seeded once with
+ * `seed` like random.seed(seed) and runs on across rays like the interpreter's global generator would.
+ * records [n][20]: r, g, b, energy, bounces, step, hits, first-hit x, y, z, flag, first-hit step, vel x, y, z, life,
+ * pos x, y, z, 0. */
+int vto_trace_rays(const vto_settings *s, const vto_camera *cam, const vto_scene *scene, const double *dirs, int64_t n,
+                   int rng_mode, uint64_t seed, double *records, uint8_t *visited, uint64_t *counters) {
+    if (!s || !cam || !scene || !dirs || !records || s->chunk_size <= 0) return 1;
+    world_t w; w.s = s; w.sc = scene; w.visited = visited;
+    int64_t nslots = 1;
+    for (int a = 0; a < 3; a++) { w.nc[a] = scene->dims[a] / s->chunk_size; nslots *= w.nc[a]; }
+    if (visited) memset(visited, 0, (size_t)nslots);
+    rng_t *g = (rng_t *)calloc(1, sizeof(rng_t));
+    g->mode = rng_mode;
+    if (rng_mode == VTO_RNG_MT19937) mt_seed_u64(&g->mt, seed);
+    uint64_t cnt[8] = { 0 };
+    for (int64_t i = 0; i < n; i++) {
+        if (rng_mode != VTO_RNG_MT19937) {
+            g->key0 = (uint32_t)i; g->key1 = (uint32_t)((uint64_t)i >> 32);
+            g->sample = 0; g->seed_lo = (uint32_t)seed; g->seed_hi = (uint32_t)(seed >> 32); g->draw = 0;
+        }
+        ray_t ray;
+        trace(&w, cam, dirs[3 * i], dirs[3 * i + 1], dirs[3 * i + 2], g, &ray, cnt);
+        double *o = records + 20 * i;
+        o[0] = ray.cr; o[1] = ray.cg; o[2] = ray.cb; o[3] = ray.energy; o[4] = ray.bounces; o[5] = ray.step;
+        o[6] = ray.hits; o[7] = (double)ray.fhit[0]; o[8] = (double)ray.fhit[1]; o[9] = (double)ray.fhit[2];
+        o[10] = ray.fflag; o[11] = ray.first_step; o[12] = ray.vel[0]; o[13] = ray.vel[1]; o[14] = ray.vel[2];
+        o[15] = ray.life; o[16] = ray.pos[0]; o[17] = ray.pos[1]; o[18] = ray.pos[2]; o[19] = 0.0;
+    }
+    if (counters) memcpy(counters, cnt, sizeof cnt);
+    free(g);
+    return 0;
+}

@@ -59,6 +59,12 @@ int vto_render(const vto_settings *s, const vto_camera *cam, const vto_scene *sc
                double *mean, uint8_t *rgba8, int32_t *nsamp, double *ray0,
                uint8_t *visited, uint64_t *counters);
 
+/* Camera.trace (init.py:37-121) for n caller-given rays: dirs [n][3] = dir_x, dir_y, detail.  records [n][20]: r, g, b,
+ * energy, bounces, step, hits, first-hit x, y, z, flag, first-hit step, vel x, y, z, life, pos x, y, z, 0.  Philox mode:
+ * ray i draws from the stream keyed i; MT19937 mode: one generator seeded with `seed` runs on across the rays. */
+int vto_trace_rays(const vto_settings *s, const vto_camera *cam, const vto_scene *scene, const double *dirs, int64_t n,
+                   int rng_mode, uint64_t seed, double *records, uint8_t *visited, uint64_t *counters);
+
 /* Known-answer hooks for the primitives (tests compare them with the imported lib.py / CPython). */
 double vto_py_floordiv(double x, double w);
 double vto_py_mod(double x, double w);

@@ -1,7 +1,7 @@
 """GpuCamera: the reference's ``Camera`` protocol (reference init.py:13-150) on top of libvoxtrace.so.
 
 Same attribute and method names as the reference class so ``Window``-style callers can swap it in:
-``pos``, ``rot``, ``lens``, ``chunks``, ``chunk_set``, ``chunk_get``, ``tile``.  The per-tile Python thread pool
+``pos``, ``rot``, ``lens``, ``chunks``, ``chunk_set``, ``chunk_get``, ``tile``, ``trace``.  The per-tile Python thread pool
 (init.py:162, 193-205) is replaced by one kernel launch per call; ``tile(thread, t)`` still returns
 ``(rgba_bytes, traversed, thread)`` like init.py:149-150.
 
@@ -409,6 +409,63 @@ class GpuCamera:
         cs = int(self.settings.chunk_size)
         idx = np.argwhere(self.visited_slots(visited_bits))
         return [tuple(int(v) for v in (i * cs + origin)) for i in idx]
+
+    # ------------------------------------------------------------------ reference protocol: trace
+    TRACE_FIELDS = ("r", "g", "b", "energy", "bounces", "step", "hits", "hit_x", "hit_y", "hit_z", "hit", "hit_step",
+                    "vel_x", "vel_y", "vel_z", "life", "pos_x", "pos_y", "pos_z")
+
+    def trace_rays(self, dirs, want=(), prepare=True):
+        """Camera.trace (init.py:37-121) for a batch: ``dirs`` [n, 3] = (dir_x, dir_y, detail) rows (numpy or tensor).
+        Returns a dict with ``records`` [n, 20] f64 on the device (columns: TRACE_FIELDS, then 0) and, when asked for in
+        ``want``, ``visited`` / ``counters`` like render().  With dof == 0 the half-angle sines and cosines are evaluated
+        here with the interpreter's own libm (math.sin / math.cos, lib.py:327-332), so the primary directions are the
+        reference's bit for bit; with dof != 0 the angles carry the per-ray lens jitter and the device evaluates them.
+        Ray i draws its jitter from the Philox stream keyed i."""
+        if prepare:
+            self._prepare()
+        s = self.settings
+        d = dirs.detach().cpu().numpy() if isinstance(dirs, torch.Tensor) else np.asarray(dirs)
+        d = np.ascontiguousarray(d, dtype=np.float64).reshape(-1, 3)
+        n = d.shape[0]
+        rec = torch.empty((n, abi.TRACE_RECORD), dtype=torch.float64, device=self.device)
+        res = {"records": rec}
+        if n == 0:
+            return res
+        sc_ptr = None
+        if float(s.dof) == 0.0:
+            prop, lens = float(s.proportions), float(self.lens)
+            sc = np.empty((n, 4), np.float64)
+            for i in range(n):                      # scalar math on purpose: numpy's vector sin / cos are not glibc's
+                rad_y = math.radians(-((d[i, 0] / prop) * lens))
+                rad_z = math.radians(+((d[i, 1] * prop) * lens))
+                sc[i] = (math.sin(rad_y / 2), math.cos(rad_y / 2), math.sin(rad_z / 2), math.cos(rad_z / 2))
+            sc_dev = torch.from_numpy(sc).to(self.device)
+            sc_ptr = sc_dev.data_ptr()
+        d_dev = torch.from_numpy(d).to(self.device)
+        self._visited.zero_()
+        self._counters.zero_()
+        self._check(self._lib.vt_trace_rays(self._ctx, d_dev.data_ptr(), sc_ptr, n, rec.data_ptr(),
+                                            self._visited.data_ptr() if "visited" in want else None,
+                                            self._counters.data_ptr() if "counters" in want else None,
+                                            int(self._frame_seed)))
+        torch.cuda.current_stream(self.device).synchronize()      # d_dev / sc_dev may be released on return
+        if "visited" in want:
+            res["visited"] = self._visited
+        if "counters" in want:
+            res["counters"] = self._counters[:8]
+        return res
+
+    def trace(self, dir_x: float, dir_y: float, detail: float):
+        """Camera.trace (init.py:37-121) for one ray; returns the ray as an attribute bag with the reference's names
+        (color, energy, pos, vel, step, life, bounces, traversed -- init.py:50-59) plus hits / first_hit.  One launch per
+        call: use trace_rays for more than a handful."""
+        from types import SimpleNamespace
+        out = self.trace_rays([(float(dir_x), float(dir_y), float(detail))], want=("visited",))
+        r = out["records"][0].cpu().numpy()
+        return SimpleNamespace(color=(int(r[0]), int(r[1]), int(r[2])), energy=float(r[3]), bounces=float(r[4]), step=float(r[5]),
+                               hits=int(r[6]), first_hit=(int(r[7]), int(r[8]), int(r[9])) if r[10] else None,
+                               vel=(float(r[12]), float(r[13]), float(r[14])), life=float(r[15]),
+                               pos=(float(r[16]), float(r[17]), float(r[18])), traversed=self.traversed(out["visited"]))
 
     # ------------------------------------------------------------------ reference protocol: tile
     def _thread_pixels(self, thread, threads):

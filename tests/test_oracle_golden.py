@@ -71,3 +71,23 @@ def test_philox_streams_are_statistically_the_references(name):
     noise = _psnr(ph, ph2)
     assert _psnr(mt, ph) >= 46.0 and abs(_psnr(mt, ph) - noise) < 1.5, (_psnr(mt, ph), noise)
     assert abs(float(np.mean(mt[:, :3] - ph[:, :3]))) < 0.15
+
+
+def test_oracle_trace_rays_matches_reference():
+    """Camera.trace called directly with arbitrary (dir_x, dir_y, detail) triples (tests/golden/trace_rays.npz, written by
+    oracle/gen_r2_golden.py from the reference): the RNG-free pass and the stochastic pass -- one MT19937 generator
+    seeded with random.seed(4242) running on across the 600 rays -- are reproduced bit for bit in the integer fields."""
+    import json
+    import os
+    from tests.golden_util import GOLDEN_DIR
+    g = np.load(os.path.join(GOLDEN_DIR, "trace_rays.npz"))
+    for tag in ("free", "stoch"):
+        sd = json.loads(str(g["settings_" + tag]))
+        world = cport.World(g["origin"], g["cells"], g["chunk_res"], g["materials_" + tag])
+        o = cport.trace_rays(sd, g["cam_pos"], g["cam_rot"], float(g["cam_lens"]), world, g["dirs"], rng=cport.RNG_MT19937,
+                             seed=int(g["seed"]))
+        ref = g["records_" + tag]
+        for cols in ([0, 1, 2], [6], [7, 8, 9, 10]):
+            assert np.array_equal(o["records"][:, cols], ref[:, cols]), (tag, cols)
+        np.testing.assert_allclose(o["records"], ref, rtol=1e-12, atol=1e-12)
+        assert np.array_equal(o["visited"], g["visited_" + tag])
