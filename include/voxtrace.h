@@ -201,7 +201,10 @@ int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t
 int vt_stream_signal_flags(vt_ctx *ctx, uint32_t *const *host_flag_ptrs, int n, uint32_t value);
 /* Same, on another CUDA stream of the context's device (e.g. the copy stream that reads the frame out). */
 int vt_stream_signal_flags_on(vt_ctx *ctx, void *cuda_stream, uint32_t *const *host_flag_ptrs, int n, uint32_t value);
-int vt_wait_status(vt_ctx *ctx, int *status);                            /* synchronises; 0 = no wait timed out */
+int vt_wait_status(vt_ctx *ctx, int *status);                            /* synchronises; 0 = no wait timed out; resets */
+/* The same word without synchronising (it lives in pinned host memory the wait kernel writes): for callers that have
+ * already waited on an event recorded after the wait.  Non-zero is reported once, then reset. */
+int vt_wait_status_peek(vt_ctx *ctx, int *status);
 int vt_copy_to_host(vt_ctx *ctx, void *host_dst, const void *dev_src, int64_t bytes);   /* async on the ctx stream */
 
 /* ---- image-space steps after the path: Window.draw_tile / Window.draw (init.py:185-190, 207-253) ----------------

@@ -20,19 +20,30 @@ class Surface:
     def __init__(self, size, flags=0):
         global LAST_SURFACE
         self.size = (int(size[0]), int(size[1]))
-        # [H, W, 4] float64; untouched pixels stay (0,0,0,0) like a fresh SRCALPHA surface
-        self.f64 = np.zeros((self.size[1], self.size[0], 4), dtype=np.float64)
+        self.px = {}                # (x, y) -> the float RGBA handed to set_at; untouched pixels are (0, 0, 0, 0)
         LAST_SURFACE = self
 
     def set_at(self, pos, color):
-        self.f64[pos[1], pos[0], :] = color
+        self.px[(int(pos[0]), int(pos[1]))] = tuple(color)
+
+    @property
+    def f64(self):
+        """[H, W, 4] float64 view of the surface (built on demand: a worker that renders a few thousand pixels of a
+        1080p window must not pay for a 66 MB array per tile, which real pygame does not either)."""
+        a = np.zeros((self.size[1], self.size[0], 4), dtype=np.float64)
+        for (x, y), c in self.px.items():
+            a[y, x, :] = c
+        return a
 
 
 class image:
     @staticmethod
     def tobytes(surface, fmt):
         assert fmt == "RGBA"
-        return np.clip(np.trunc(surface.f64), 0, 255).astype(np.uint8).tobytes()
+        a = np.zeros((surface.size[1], surface.size[0], 4), dtype=np.uint8)      # fresh SRCALPHA surface: all zero
+        for (x, y), c in surface.px.items():
+            a[y, x, :] = np.clip(np.trunc(np.asarray(c, dtype=np.float64)), 0, 255).astype(np.uint8)
+        return a.tobytes()
 
 
 class time:

@@ -26,6 +26,7 @@ import numpy as np
 
 REFERENCE_ROOT = os.environ.get("VT_REFERENCE_ROOT", "/root/reference")
 _STUB_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "pygame_stub")
+BYTECODE_ROOT = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")     # oracle/build_ref.py
 
 _REF = None
 
@@ -34,33 +35,48 @@ def available() -> bool:
     return os.path.isfile(os.path.join(REFERENCE_ROOT, "init.py"))
 
 
+def available_bytecode() -> bool:
+    """oracle/_ref/ (bytecode of the reference built by oracle/build_ref.py) is present and was compiled by this
+    interpreter version."""
+    import importlib.util
+    stamp = os.path.join(BYTECODE_ROOT, "BUILT_WITH")
+    if not os.path.isfile(stamp) or not os.path.isfile(os.path.join(BYTECODE_ROOT, "vt_reference_init.pyc")):
+        return False
+    return open(stamp).read().strip().endswith(importlib.util.MAGIC_NUMBER.hex())
+
+
 def load_reference(mod: str = "default"):
     """Import the reference once per process; returns a namespace (data, lib, Camera, Window, pg)."""
     global _REF
     if _REF is not None:
         return _REF
-    if not available():
-        raise RuntimeError("reference tree not present at %s" % REFERENCE_ROOT)
+    from_source = available()
+    if not from_source and not available_bytecode():
+        raise RuntimeError("reference tree not present at %s (and no bytecode build under %s)" % (REFERENCE_ROOT, BYTECODE_ROOT))
+    root = REFERENCE_ROOT if from_source else BYTECODE_ROOT
     sys.dont_write_bytecode = True
-    for p in (_STUB_DIR, REFERENCE_ROOT):
+    for p in (_STUB_DIR, root):
         if p not in sys.path:
             sys.path.insert(0, p)
     old_cwd, old_argv = os.getcwd(), sys.argv
-    os.chdir(REFERENCE_ROOT)
+    os.chdir(root)
     sys.argv = ["init.py", mod]
     try:
         import pygame as pg  # the stub
         import lib
         import data
-        with open(os.path.join(REFERENCE_ROOT, "init.py"), "rt") as f:
-            tree = ast.parse(f.read())
-        keep = [n for n in tree.body
-                if isinstance(n, (ast.Import, ast.ImportFrom))
-                or (isinstance(n, ast.ClassDef) and n.name in ("Camera", "Window"))]
-        module = types.ModuleType("vt_reference_init")
-        module.__file__ = os.path.join(REFERENCE_ROOT, "init.py")
-        sys.modules["vt_reference_init"] = module
-        exec(compile(ast.Module(body=keep, type_ignores=[]), module.__file__, "exec"), module.__dict__)
+        if from_source:
+            with open(os.path.join(REFERENCE_ROOT, "init.py"), "rt") as f:
+                tree = ast.parse(f.read())
+            keep = [n for n in tree.body
+                    if isinstance(n, (ast.Import, ast.ImportFrom))
+                    or (isinstance(n, ast.ClassDef) and n.name in ("Camera", "Window"))]
+            module = types.ModuleType("vt_reference_init")
+            module.__file__ = os.path.join(REFERENCE_ROOT, "init.py")
+            sys.modules["vt_reference_init"] = module
+            exec(compile(ast.Module(body=keep, type_ignores=[]), module.__file__, "exec"), module.__dict__)
+        else:                                   # the same extraction, done at build time by oracle/build_ref.py
+            import vt_reference_init as module
     finally:
         os.chdir(old_cwd)
         sys.argv = old_argv
@@ -188,7 +204,7 @@ def _tile_worker(t):
         del cam.trace
     surf = ref.pg.LAST_SURFACE
     px = ref.data.settings.pixels[t]
-    means = np.array([surf.f64[y, x] for (x, y) in px], dtype=np.float64).reshape(-1, 4)
+    means = np.array([surf.px.get((x, y), (0.0, 0.0, 0.0, 0.0)) for (x, y) in px], dtype=np.float64).reshape(-1, 4)
     return t, means, np.array(rays, dtype=np.float64).reshape(-1, 15), [tuple(c) for c in traversed]
 
 

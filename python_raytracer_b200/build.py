@@ -17,6 +17,17 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
               "-shared", "-Xcompiler", "-fPIC", "-lz"]
 
 
+def kernel_source_sha256() -> str:
+    """sha256 over the CUDA / C++ sources and the ABI header: ties a committed ncu capture to the kernel it was taken
+    from (profiles/r*_traffic.json carry it, bench.py reports `traffic_stale` when it differs)."""
+    import hashlib
+    h = hashlib.sha256()
+    for path in sorted([os.path.join(CSRC, s) for s in SOURCES] + HEADERS):
+        with open(path, "rb") as f:
+            h.update(os.path.basename(path).encode() + b"\0" + f.read())
+    return h.hexdigest()
+
+
 def _nvcc() -> str:
     exe = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
     if not os.path.exists(exe):

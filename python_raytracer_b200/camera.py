@@ -349,11 +349,12 @@ class GpuCamera:
             self._visited = torch.zeros(nwords, dtype=torch.int32, device=self.device)
 
     def render(self, pixels=None, rect=None, stripes=(1, 1, 0), want=("rgba8",), prepare=True, out=None,
-               clear=True):
+               clear=True, visited_out=None):
         """One pass of the hot path.  ``pixels``: [n,2] int32 (x,y) list (numpy / tensor) or None for the rectangle
         ``rect`` = (x0, y0, x1, y1) (default: whole canvas) restricted to rows whose stripe
         (y // stripes[0]) % stripes[1] == stripes[2].  ``want`` picks outputs among rgba8, mean, ray0, visited,
-        counters.  Returns a dict of CUDA tensors (nothing is copied to the host here)."""
+        counters.  ``visited_out``: an int32 word tensor to OR the visited bits into instead of the camera's own (the
+        caller clears it).  Returns a dict of CUDA tensors (nothing is copied to the host here)."""
         if prepare:
             self._prepare()
         s = self.settings
@@ -378,17 +379,19 @@ class GpuCamera:
                 if name not in res:
                     res[name] = torch.empty(shape + tail, dtype=dt, device=self.device)
                 ptr[name] = res[name].data_ptr()
+        vis = self._visited if visited_out is None else visited_out
         if clear:
-            self._visited.zero_()
+            if visited_out is None:
+                self._visited.zero_()
             self._counters.zero_()
         self._check(self._lib.vt_render(self._ctx, C.byref(reg), ptr.get("rgba8"), ptr.get("mean"), ptr.get("ray0"),
-                                        self._visited.data_ptr() if "visited" in want else None,
+                                        vis.data_ptr() if "visited" in want else None,
                                         self._counters.data_ptr() if "counters" in want else None,
                                         int(self._frame_seed)))
         if not s.static:
             self._frame_seed += 1
         if "visited" in want:
-            res["visited"] = self._visited
+            res["visited"] = vis
         if "counters" in want:
             res["counters"] = self._counters[:8]
             res["trips"] = self._counters[8:14]          # phase trip counts, only filled by a VT_TRIPS build (tools/kbench.py)

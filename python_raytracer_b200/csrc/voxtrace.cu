@@ -25,7 +25,7 @@ __global__ void wait_flags_kernel(const unsigned int *flags, int n, unsigned int
     if (t >= n) return;
     const long long t0 = clock64();
     while ((int)(*(volatile const unsigned int *)(flags + t) - value) < 0) {
-        if (clock64() - t0 > timeout_cycles) { atomicExch(status, 1 + t); return; }
+        if (clock64() - t0 > timeout_cycles) { *(volatile int *)status = 1 + t; __threadfence_system(); return; }
         __nanosleep(200);
     }
     __threadfence_system();
@@ -181,7 +181,8 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     cudaStreamSynchronize(ctx->stream);
     free_world(ctx);
     cudaFree(ctx->d_mats); cudaFree(ctx->d_col_sc); cudaFree(ctx->d_row_sc); cudaFree(ctx->d_row_y);
-    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_pow_tab); cudaFree(ctx->d_wait_status);
+    cudaFree(ctx->d_acc); cudaFree(ctx->d_queue); cudaFree(ctx->d_pow_tab);
+    if (ctx->d_wait_status) cudaFreeHost(ctx->d_wait_status);
     for (int k = 0; k < 4; k++) cudaFree(ctx->fx_buf[k]);
     for (int k = 0; k < 3; k++) cudaFree(ctx->scene_buf[k]);
     if (ctx->h_word) cudaFreeHost(ctx->h_word);
@@ -685,9 +686,9 @@ extern "C" int vt_set_visited_peer(vt_ctx *ctx, uint32_t *dev_peer_mask, int64_t
 extern "C" int vt_stream_wait_flags(vt_ctx *ctx, const uint32_t *dev_flags, int n, uint32_t value, double timeout_s) {
     if (!ctx || !dev_flags || n < 1 || n > 32) return 1;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    if (!ctx->d_wait_status) {
-        VT_CHECK(ctx, cudaMalloc(&ctx->d_wait_status, sizeof(int)));
-        VT_CHECK(ctx, cudaMemsetAsync(ctx->d_wait_status, 0, sizeof(int), ctx->stream));
+    if (!ctx->d_wait_status) {                 // pinned host word the wait kernel writes on a timeout: the host reads it without a CUDA call
+        VT_CHECK(ctx, cudaHostAlloc(&ctx->d_wait_status, sizeof(int), cudaHostAllocMapped));
+        *ctx->d_wait_status = 0;
     }
     if (ctx->clock_khz == 0) {                 // queried once: this attribute is slow to read (~1 ms)
         int khz = 0;
@@ -719,8 +720,15 @@ extern "C" int vt_wait_status(vt_ctx *ctx, int *status) {
     *status = 0;
     if (!ctx->d_wait_status) return 0;
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
-    VT_CHECK(ctx, cudaMemcpyAsync(status, ctx->d_wait_status, sizeof(int), cudaMemcpyDeviceToHost, ctx->stream));
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    *status = *(volatile int *)ctx->d_wait_status;
+    *ctx->d_wait_status = 0;
+    return 0;
+}
+extern "C" int vt_wait_status_peek(vt_ctx *ctx, int *status) {
+    if (!ctx || !status) return 1;
+    *status = ctx->d_wait_status ? *(volatile int *)ctx->d_wait_status : 0;
+    if (*status) *ctx->d_wait_status = 0;
     return 0;
 }
 extern "C" int vt_copy_to_host(vt_ctx *ctx, void *host_dst, const void *dev_src, int64_t bytes) {

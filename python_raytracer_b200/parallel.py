@@ -149,8 +149,11 @@ class PeerFrameRenderer:
     """
 
     FLAGS_PER_BUFFER = 32
+    VIS_RING = 8          # visited-union masks in rank 0's memory, one per frame modulo 8 (see render_frame)
 
-    def __init__(self, cam, rank: int, world: int, stripe: int = STRIPE_ROWS, buffers: int = 2):
+    def __init__(self, cam, rank: int, world: int, stripe: int = STRIPE_ROWS, buffers: int = 2, visited_words: int = 0):
+        """visited_words > 0 (u32 words of the camera's visited-chunk bitmask) enables the culling union: rank 0 then also
+        owns VIS_RING masks of that size which the render kernels OR their visited bits into (render_frame(visited=True))."""
         import ctypes as C
         self.cam, self.rank, self.world, self.stripe, self.buffers = cam, rank, world, stripe, buffers
         self.w, self.h = int(cam.settings.width), int(cam.settings.height)
@@ -158,7 +161,8 @@ class PeerFrameRenderer:
         self._C = C
         lib, ctx = cam._lib, cam._ctx
         nbytes = self.w * self.h * 4
-        mine = []                      # (kind, ptr) owned by this rank
+        self.visited_words = int(visited_words)
+        self.vis_ring = None
         handles = {}
         if rank == 0:
             self.frames = []
@@ -169,7 +173,15 @@ class PeerFrameRenderer:
             p = C.c_void_p()
             cam._check(lib.vt_shared_alloc(ctx, 4 * self.FLAGS_PER_BUFFER * buffers, C.byref(p)))
             self.arrive = p.value
-            for k, ptr in enumerate(self.frames + [self.arrive]):
+            shared = self.frames + [self.arrive]
+            if self.visited_words:
+                p = C.c_void_p()
+                cam._check(lib.vt_shared_alloc(ctx, 4 * self.visited_words * self.VIS_RING, C.byref(p)))
+                self.vis_ring = p.value
+                shared.append(self.vis_ring)
+                self.vis_views = [torch.as_tensor(_DevView(self.vis_ring + 4 * self.visited_words * k, (self.visited_words,), "<i4"),
+                                                  device=cam.device) for k in range(self.VIS_RING)]
+            for k, ptr in enumerate(shared):
                 hb = C.create_string_buffer(64)
                 cam._check(lib.vt_ipc_export(ctx, C.c_void_p(ptr), hb))
                 handles[k] = hb.raw
@@ -196,34 +208,76 @@ class PeerFrameRenderer:
                 self._opened.append(q.value)
         else:
             self.frames = []
-            for k in range(buffers + 1):
+            for k in range(buffers + 1 + (1 if self.visited_words else 0)):
                 q = C.c_void_p()
                 cam._check(lib.vt_ipc_open(ctx, gathered[0][k], C.byref(q)))
                 self._opened.append(q.value)
-                (self.frames.append(q.value) if k < buffers else setattr(self, "arrive", q.value))
+                if k < buffers:
+                    self.frames.append(q.value)
+                elif k == buffers:
+                    self.arrive = q.value
+                else:
+                    self.vis_ring = q.value
 
     def _flag(self, b, r):
         return self.arrive + 4 * (b * self.FLAGS_PER_BUFFER + r)
 
-    def render_frame(self, prepare=True):
-        """Renders this rank's stripes of the next frame into rank 0's frame buffer.  Returns the buffer index."""
+    def render_frame(self, prepare=True, visited=False):
+        """Renders this rank's stripes of the next frame into rank 0's frame buffer.  Returns the buffer index.
+
+        visited=True (culling): the union of every rank's visited-chunk bits (the reference merges the workers'
+        traversed lists every frame, init.py:189, 393) is assembled in rank 0's memory by the render kernels themselves.
+        Rank 0 marks straight into mask f % VIS_RING, the other ranks mark a local mask and their launch's last warp ORs
+        its non-zero words into the same mask over NVLink before the arrival flag goes up, so once rank 0 has seen the
+        flags it holds the union (``visited_union``).  Mask (f + 4) % 8 is cleared by rank 0 ahead of time: ranks are
+        never more than ``buffers`` frames apart (frame credits), so nobody writes it yet and nobody reads it any more."""
         C = self._C
         cam, lib, ctx = self.cam, self.cam._lib, self.cam._ctx
         f = self.frame_no
         b, k = f % self.buffers, f // self.buffers
         if prepare:
             cam._prepare()
+        if visited and not self.visited_words:
+            raise RuntimeError("PeerFrameRenderer was built without visited_words")
+        if visited and cam._visited.numel() != self.visited_words:
+            raise RuntimeError("the camera's chunk grid changed: %d visited words, the shared masks hold %d" % (cam._visited.numel(), self.visited_words))
         if self.rank > 0 and k > 0:            # buffer b must have been released k times by rank 0
             cam._check(lib.vt_stream_wait_flags(ctx, C.c_void_p(self.credit + 4 * b), 1, k, 30.0))
         cam._check(lib.vt_set_frame_target(ctx, C.c_void_p(self.frames[b]), C.c_void_p(self._flag(b, self.rank)), f + 1))
+        slot = f % self.VIS_RING
+        vis_out = None
+        if visited:
+            if self.rank == 0:
+                self.vis_views[(f + self.VIS_RING // 2) % self.VIS_RING].zero_()
+                vis_out = self.vis_views[slot]
+            else:
+                cam._check(lib.vt_set_visited_peer(ctx, C.c_void_p(self.vis_ring + 4 * self.visited_words * slot), self.visited_words))
         try:
-            cam.render(stripes=(self.stripe, self.world, self.rank), want=(), prepare=False)
+            cam.render(stripes=(self.stripe, self.world, self.rank), want=("visited",) if visited else (), prepare=False,
+                       visited_out=vis_out)
         finally:
             cam._check(lib.vt_set_frame_target(ctx, None, None, 0))
+            if visited and self.rank > 0:
+                cam._check(lib.vt_set_visited_peer(ctx, None, 0))
         if self.rank == 0 and self.world > 1:
             cam._check(lib.vt_stream_wait_flags(ctx, C.c_void_p(self._flag(b, 1)), self.world - 1, f + 1, 30.0))
+        self._last_visited_slot = slot if visited else None
         self.frame_no += 1
         return b
+
+    def visited_union(self):
+        """The union of all ranks' visited bits of the last render_frame(visited=True), as an int32 word tensor on
+        EVERY rank (rank 0 holds it once the arrival flags are in; the others get it by one small broadcast -- the
+        chunk update that consumes it is host logic on every rank, init.py:446-452)."""
+        if getattr(self, "_last_visited_slot", None) is None:
+            raise RuntimeError("visited_union: the last frame was not rendered with visited=True")
+        if self.rank == 0:
+            t = self.vis_views[self._last_visited_slot].clone()
+        else:
+            t = torch.empty(self.visited_words, dtype=torch.int32, device=self.cam.device)
+        if self.world > 1:
+            dist.broadcast(t, src=0)
+        return t
 
     def release(self, b):
         """Rank 0: frame buffer b has been consumed (stream-ordered); the renderers may overwrite it."""
@@ -244,6 +298,7 @@ class PeerFrameRenderer:
             host_rgba8.copy_(self.frame_views[b], non_blocking=True)
             self.release(b)
             torch.cuda.current_stream(self.cam.device).synchronize()
+            self._check_waits()
         return host_rgba8
 
     # ---- pipelined variant: rank 0 reads frame b out on a copy stream while everybody renders frame b + 1 --------
@@ -277,10 +332,19 @@ class PeerFrameRenderer:
         self._pipe["copied"][b] = ev
         return ev
 
-    @staticmethod
-    def wait(ticket):
+    def wait(self, ticket):
         if ticket is not None:
             ticket.synchronize()
+            self._check_waits()
+
+    def _check_waits(self):
+        """A flag wait that gave up (a peer that never arrived) must not hand a torn frame to the caller silently."""
+        C = self._C
+        st = C.c_int(0)
+        self.cam._check(self.cam._lib.vt_wait_status_peek(self.cam._ctx, C.byref(st)))
+        if st.value:
+            from .abi import VoxtraceError
+            raise VoxtraceError("rank %d: a flag wait timed out (flag index %d): a peer did not deliver its part of the frame" % (self.rank, st.value - 1))
 
     def wait_status(self) -> int:
         C = self._C
@@ -299,7 +363,8 @@ class PeerFrameRenderer:
             dist.barrier()
         if self.rank == 0:
             self.frame_views = None
-            for p in self.frames + [self.arrive]:
+            self.vis_views = None
+            for p in self.frames + [self.arrive] + ([self.vis_ring] if self.vis_ring else []):
                 lib.vt_shared_free(ctx, C.c_void_p(p))
         else:
             lib.vt_shared_free(ctx, C.c_void_p(self.credit))

@@ -1,4 +1,5 @@
-"""Multi-GPU check of the peer-memory frame path (run under torchrun on a box with >= 2 GPUs; not collected by pytest):
+"""Multi-GPU check of the peer-memory frame path (run under torchrun on a box with >= 2 GPUs; tests/test_gpu_multi.py
+launches it when the box has them):
    torchrun --nproc-per-node N tests/mgpu_peer_check.py
 Every rank renders its stripes straight into rank 0's frame; rank 0 compares 6 frames (two buffers, three rounds, the
 camera moving) with its own single-GPU render of the same frames and with the NCCL-gather path, bit for bit."""
@@ -64,14 +65,64 @@ def main():
                 bad += not ok
         prev = tk
     st = peer.wait_status()
-    t = torch.tensor([bad + (st != 0)], device=dev)
-    dist.all_reduce(t)
     peer.close()
     cam.close()
+    bad += culling_check(rank, world, local)
+    t = torch.tensor([bad + (st != 0)], device=dev)
+    dist.all_reduce(t)
     dist.destroy_process_group()
     if rank == 0:
         print("PEER CHECK", "OK" if int(t) == 0 else "FAILED", flush=True)
     sys.exit(0 if int(t) == 0 else 1)
+
+
+def culling_check(rank, world, local):
+    """C5 (9.9 M-voxel model, 1080p 8 spp, culling on) split over the ranks through the fused path: every rank's visited
+    bits reach rank 0's mask over NVLink with the arrival flag, every rank applies the same chunk update
+    (init.py:446-452), and after the same warm-up the N-GPU frames, visited unions and resident-chunk sets are the ones a
+    single GPU produces."""
+    from python_raytracer_b200.builder import SceneObject, WorldBuilder
+    from python_raytracer_b200.mathutil import euler_to_quaternion
+    from python_raytracer_b200.scenes import C5_EULER, C5_MATERIALS, C5_POS, C5_SETTINGS, C5_SIZE, goxel_model_grid
+    sd = dict(C5_SETTINGS); sd["threads"] = 1
+    grid = goxel_model_grid(C5_SIZE)
+    cams, builders = [], []
+    for _ in range(2 if rank == 0 else 1):                 # rank 0 keeps a second, single-GPU camera as the yardstick
+        cam = GpuCamera(Settings.from_object(sd), device=local, background_function=bench.BUILTIN_BG, background=bench.BUILTIN_BG)
+        cam.pos, cam.rot = C5_POS, euler_to_quaternion(*C5_EULER)
+        wb = WorldBuilder(cam)
+        wb.build([SceneObject(sprite=grid, pos=(0.0, 0.0, 0.0))], C5_MATERIALS)
+        wb.update_lod(visible=None)
+        cams.append(cam); builders.append(wb)
+    cam, wb = cams[0], builders[0]
+    cam._prepare()
+    peer = PeerFrameRenderer(cam, rank, world, visited_words=cam._visited.numel())
+    host = torch.empty((sd["height"], sd["width"], 4), dtype=torch.uint8).pin_memory()
+    bad = 0
+    for f in range(5):
+        b = peer.render_frame(prepare=True, visited=True)
+        union = peer.visited_union()
+        if rank == 0:
+            host.copy_(peer.frame_views[b])
+            peer.release(b)
+        torch.cuda.synchronize()
+        vis = cam.visited_slots(union).copy()
+        res = wb.update_lod(visible=vis)
+        if rank == 0:
+            c1, w1 = cams[1], builders[1]
+            out = c1.render(want=("rgba8", "visited"))
+            torch.cuda.synchronize()
+            vis1 = c1.visited_slots(out["visited"]).copy()
+            res1 = w1.update_lod(visible=vis1)
+            ok = torch.equal(out["rgba8"].cpu(), host) and np.array_equal(vis, vis1) and np.array_equal(res, res1)
+            print("culling frame %d: frame, visited union (%d chunks) and resident set (%d chunks) == single GPU: %s" % (
+                f, int(vis.sum()), int((res > 0).sum()), ok), flush=True)
+            bad += not ok
+    bad += peer.wait_status() != 0
+    peer.close()
+    for c in cams:
+        c.close()
+    return bad
 
 
 if __name__ == "__main__":

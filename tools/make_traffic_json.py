@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Per-launch DRAM traffic and issue statistics of the render kernel from a tools/ncu_summary.py text -> the JSON
-bench.py reads for roofline.traffic (profiles/r1_traffic.json):  python tools/make_traffic_json.py summary.txt <name to cite>"""
+bench.py reads for roofline.traffic (profiles/r*_traffic.json):
+   python tools/make_traffic_json.py summary.txt <name to cite> [sha256 of the kernel sources the capture was taken from]"""
 import json, re, sys
 txt = open(sys.argv[1]).read()
 cite = sys.argv[2] if len(sys.argv) > 2 else sys.argv[1]
@@ -32,6 +33,7 @@ rd = [to_bytes(b, "dram__bytes_read.sum") for b in launches]
 wr = [to_bytes(b, "dram__bytes_write.sum") for b in launches]
 out = {
     "kernel": "render_persistent<FAST>",
+    **({"kernel_sha256": sys.argv[3]} if len(sys.argv) > 3 else {}),
     "source": "%s (ncu --set full --clock-control none, bench.py --steps 4 --warmup 3, the four timed launches = the four camera poses)" % cite,
     "dram_read_bytes_per_launch": rd,
     "dram_write_bytes_per_launch": wr,
