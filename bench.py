@@ -166,8 +166,8 @@ def port_baseline(sd, origin, cells, mats, poses, stride, steps, what):
     cores = os.cpu_count() or 1
     v, rays_step, secs = oracle_rays_per_sec(sd, origin, cells, mats, poses, stride, steps, 1, cores)
     return {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "seconds": round(secs, 2),
-            "sample": "%d frames, every %s pixel in x and y of %s (%d rays each), C port of the reference trace loop "
-                      "(oracle/vt_oracle.c), %d threads" % (steps, _ordinal(stride), what, rays_step, cores)}
+            "sample": "%d frames, %s of %s (%d rays each), C port of the reference trace loop (oracle/vt_oracle.c), %d threads" % (
+                steps, "every pixel" if stride == 1 else "every %s pixel in x and y" % _ordinal(stride), what, rays_step, cores)}
 
 
 def _ordinal(n):
@@ -514,7 +514,7 @@ def run_ours(args, rank, world, local_rank):
     if rank == 0:
         line["clocks"] = sampler.stop() if sampler else None
         if world == 1 and not args.no_cpu_baseline:
-            line["cpu_baseline"] = port_baseline(C3_SETTINGS, origin, cells, mats, poses, 3, 4, "1920x1080x4spp, one frame per pose")
+            line["cpu_baseline"] = port_baseline(C3_SETTINGS, origin, cells, mats, poses, 1, 8, "1920x1080x4spp, two frames per pose")
             line["cpu_baselines"] = [line["cpu_baseline"]]
             if reference_available():
                 try:
@@ -575,7 +575,7 @@ def config_c4(args, torch, dist, dev, rank, world, local_rank, use_peer, flush, 
            "frame_crc": crcs, "frame_crc_1gpu": alone, "identical_to_1gpu": same_frames(crcs, alone)}
     if world == 1 and not args.no_cpu_baseline:
         pp = [dict(pos=p["pos"], rot=p["rot"], chunk_res=res) for p in poses]
-        out["cpu_baseline"] = port_baseline(sd, origin, cells, mats, pp, 16, 2, "3840x2160x16spp")
+        out["cpu_baseline"] = port_baseline(sd, origin, cells, mats, pp, 4, 4, "3840x2160x16spp, one frame per pose")
     return out
 
 
@@ -629,7 +629,7 @@ def config_c5(args, torch, dist, dev, rank, world, local_rank, use_peer, flush, 
            "frame_crc": crcs, "frame_crc_1gpu": alone, "identical_to_1gpu": same_frames(crcs, alone)}
     if world == 1 and not args.no_cpu_baseline:
         pp = [dict(pos=C5_POS, rot=rot, chunk_res=res)]
-        out["cpu_baseline"] = port_baseline(sd, wb.origin.astype(np.int32), cells.cpu().numpy(), C5_MATERIALS, pp, 8, 2, "1920x1080x8spp")
+        out["cpu_baseline"] = port_baseline(sd, wb.origin.astype(np.int32), cells.cpu().numpy(), C5_MATERIALS, pp, 2, 4, "1920x1080x8spp")
     cam.close()
     return out
 
