@@ -5,8 +5,10 @@ bench.py can time the reference's own Python trace loop on the box's host cores 
 
 Output goes to oracle/_ref/ only -- git-ignored, not gpurun-ignored, so it travels to the box like the built .so files --
 and consists of BYTECODE compiled from the sources where they lie plus the default mod's data files:
-  lib.pyc, data.pyc, mods/default/init.pyc     py_compile of the reference files
-  vt_reference_init.pyc                        the imports + class Camera + class Window of init.py (its last line opens a
+  lib.vtbc, data.vtbc, mods/default/init.vtbc  py_compile of the reference files (pyc content; the extension is not .pyc
+                                               because the gpurun snapshot leaves *.pyc behind -- refharness loads them
+                                               through its own finder)
+  vt_reference_init.vtbc                       the imports + class Camera + class Window of init.py (its last line opens a
                                                window, init.py:474), extracted from the AST exactly as refharness does
   mods/default/config.cfg, mods/default/voxels/*.gz   the mod's configuration and voxel models (data, read at import)
 No reference source text is copied.  TEST INFRASTRUCTURE ONLY.
@@ -36,14 +38,14 @@ def build(force: bool = False) -> str | None:
     shutil.rmtree(OUT, ignore_errors=True)
     os.makedirs(os.path.join(OUT, "mods", "default", "voxels"))
     for rel in ("lib.py", "data.py", os.path.join("mods", "default", "init.py")):
-        py_compile.compile(os.path.join(src, rel), cfile=os.path.join(OUT, rel + "c"), dfile=rel, doraise=True)
+        py_compile.compile(os.path.join(src, rel), cfile=os.path.join(OUT, rel[:-3] + ".vtbc"), dfile=rel, doraise=True)
     with open(os.path.join(src, "init.py"), "rt") as f:
         tree = ast.parse(f.read())
     keep = [n for n in tree.body if isinstance(n, (ast.Import, ast.ImportFrom))
             or (isinstance(n, ast.ClassDef) and n.name in ("Camera", "Window"))]
     code = compile(ast.Module(body=keep, type_ignores=[]), "init.py", "exec")
     from importlib._bootstrap_external import _code_to_timestamp_pyc
-    with open(os.path.join(OUT, "vt_reference_init.pyc"), "wb") as f:
+    with open(os.path.join(OUT, "vt_reference_init.vtbc"), "wb") as f:
         f.write(_code_to_timestamp_pyc(code, 0, 0))
     shutil.copy(os.path.join(src, "mods", "default", "config.cfg"), os.path.join(OUT, "mods", "default", "config.cfg"))
     vox = os.path.join(src, "mods", "default", "voxels")

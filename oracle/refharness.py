@@ -40,9 +40,33 @@ def available_bytecode() -> bool:
     interpreter version."""
     import importlib.util
     stamp = os.path.join(BYTECODE_ROOT, "BUILT_WITH")
-    if not os.path.isfile(stamp) or not os.path.isfile(os.path.join(BYTECODE_ROOT, "vt_reference_init.pyc")):
+    if not os.path.isfile(stamp) or not os.path.isfile(os.path.join(BYTECODE_ROOT, "vt_reference_init.vtbc")):
         return False
     return open(stamp).read().strip().endswith(importlib.util.MAGIC_NUMBER.hex())
+
+
+class _BytecodeFinder:
+    """Imports the reference's modules from the bytecode files of oracle/_ref/ (oracle/build_ref.py)."""
+    FILES = {"lib": "lib.vtbc", "data": "data.vtbc", "vt_reference_init": "vt_reference_init.vtbc",
+             "mods.default.init": os.path.join("mods", "default", "init.vtbc")}
+
+    def find_spec(self, fullname, path=None, target=None):
+        import importlib.util
+        rel = self.FILES.get(fullname)
+        if rel is None or not os.path.isfile(os.path.join(BYTECODE_ROOT, rel)):
+            return None
+        return importlib.util.spec_from_loader(fullname, self, origin=os.path.join(BYTECODE_ROOT, rel))
+
+    def create_module(self, spec):
+        return None
+
+    def exec_module(self, module):
+        import marshal
+        path = os.path.join(BYTECODE_ROOT, self.FILES[module.__name__])
+        with open(path, "rb") as f:
+            code = marshal.loads(f.read()[16:])          # pyc: 16-byte header, then the marshalled code object
+        module.__file__ = path
+        exec(code, module.__dict__)
 
 
 def load_reference(mod: str = "default"):
@@ -54,6 +78,8 @@ def load_reference(mod: str = "default"):
     if not from_source and not available_bytecode():
         raise RuntimeError("reference tree not present at %s (and no bytecode build under %s)" % (REFERENCE_ROOT, BYTECODE_ROOT))
     root = REFERENCE_ROOT if from_source else BYTECODE_ROOT
+    if not from_source and not any(isinstance(f, _BytecodeFinder) for f in sys.meta_path):
+        sys.meta_path.insert(0, _BytecodeFinder())
     sys.dont_write_bytecode = True
     for p in (_STUB_DIR, root):
         if p not in sys.path:

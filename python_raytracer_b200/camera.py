@@ -77,7 +77,7 @@ class GpuCamera:
         self._settings_key = None
         self._frame_seed = 0
         self._visited = None
-        self._counters = torch.zeros(16, dtype=torch.int64, device=self.device)
+        self._counters = torch.zeros(32, dtype=torch.int64, device=self.device)
         self._pix_cache = {}
         self._static_materials = None
         self._mats_sent = None
@@ -394,7 +394,7 @@ class GpuCamera:
             res["visited"] = vis
         if "counters" in want:
             res["counters"] = self._counters[:8]
-            res["trips"] = self._counters[8:14]          # phase trip counts, only filled by a VT_TRIPS build (tools/kbench.py)
+            res["trips"] = self._counters[8:26]          # phase trip counts and cycles, only filled by a VT_TRIPS build (tools/kbench.py)
         return res
 
     def visited_slots(self, visited_bits) -> np.ndarray:

@@ -35,6 +35,9 @@
 #ifndef VT_INVN
 #define VT_INVN 1                    // pixel mean by an exact reciprocal multiply when the sample count is a power of two
 #endif
+#ifndef VT_COLD_SMEM
+#define VT_COLD_SMEM 1               // per-ray state the march loops never touch lives in shared memory, not in registers
+#endif
 #ifndef VT_MINB
 #define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
 #endif
@@ -49,15 +52,35 @@ __device__ __forceinline__ double pmin(double a, double b) { return b < a ? b : 
 __device__ __forceinline__ double pmax(double a, double b) { return b > a ? b : a; }
 
 // st: bits 0-1 state, bits 2-9 material id of a pending hit, bits 12-31 sample index of the ray
+// Hot state (touched by every sample: 8 doubles + 5 words = 21 registers) and cold state (touched when a ray starts, is
+// shaded or ends: 2 doubles + 6 words).  At 48 warps per SM the kernel has 40 registers per thread; with everything in
+// registers ptxas spilled ~430 bytes per thread.  The cold fields therefore live in shared memory (structure of arrays,
+// 40 bytes per thread, 60 KB per SM at 12 blocks): they are reference members, so the code below reads the same either
+// way (-DVT_COLD_SMEM=0 puts them back into registers for an A/B: 1.760 vs 1.755 ms/frame, spill stores 406 -> 278 B).
+struct ColdStore {
+    double bounces[128], energy[128];
+    int col[128];
+    uint32_t xy[128], out_i[128], draw[128], w2[128], w3[128];
+};
 struct Lane {
-    double px, py, pz, vx, vy, vz, step, life, bounces, energy;
-    int col;                        // ray.color as r | g << 8 | b << 16 (integers, lib.py:393-395)
+    double px, py, pz, vx, vy, vz, step, life;
     int cx, cy, cz;                 // chunk_min relative to the world origin (chunk_max = chunk_min + chunk_size)
     int res;                        // Frame.resolution of the current chunk, 0 = `chunk is None`
     uint32_t st;
-    uint32_t xy;                    // pixel x | y << 16
-    uint32_t out_i;                 // output index of the pixel
-    uint32_t draw, w2, w3;          // Philox draw counter and the cached second uniform of the last block
+#if VT_COLD_SMEM
+    double &bounces, &energy;
+    int &col;                       // ray.color as r | g << 8 | b << 16 (integers, lib.py:393-395)
+    uint32_t &xy;                   // pixel x | y << 16
+    uint32_t &out_i;                // output index of the pixel
+    uint32_t &draw, &w2, &w3;       // Philox draw counter and the cached second uniform of the last block
+    __device__ __forceinline__ Lane(ColdStore &s, int t)
+        : bounces(s.bounces[t]), energy(s.energy[t]), col(s.col[t]), xy(s.xy[t]), out_i(s.out_i[t]), draw(s.draw[t]), w2(s.w2[t]), w3(s.w3[t]) {}
+#else
+    double bounces, energy;
+    int col;
+    uint32_t xy, out_i, draw, w2, w3;
+    __device__ __forceinline__ Lane(ColdStore &, int) {}
+#endif
 };
 
 struct FirstHit {                   // parity probe state, only live in the REC instantiation
@@ -658,7 +681,12 @@ template <bool FAST, bool REC, bool FULL_TAIL, bool COUNT>
 __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_constant__ DevParams P, const int32_t *__restrict__ row_y) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    Lane L;
+#if VT_COLD_SMEM
+    __shared__ ColdStore cold;
+#else
+    ColdStore &cold = *(ColdStore *)nullptr;
+#endif
+    Lane L(cold, threadIdx.x);
     L.st = ST_NONE; L.px = L.py = L.pz = L.vx = L.vy = L.vz = 0.0; L.step = L.life = L.bounces = L.energy = 0.0;
     L.col = 0; L.cx = L.cy = L.cz = 0; L.res = 0; L.xy = 0; L.out_i = 0; L.draw = L.w2 = L.w3 = 0;
     FirstHit fh; fh.hits = fh.fflag = fh.fx = fh.fy = fh.fz = 0; fh.first_step = -1.0;
@@ -666,6 +694,13 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
     unsigned rays = 0;
 #if VT_TRIPS
     unsigned trips[6] = {0, 0, 0, 0, 0, 0};   // march trips, shade trips, shade lanes, refill trips, refill lanes, march phases
+    long long cyc[4] = {0, 0, 0, 0}, tc0 = 0;  // cycles of this warp in refill, shade, march, block A of march
+    long long bk[8] = {0, 0, 0, 0, 0, 0, 0, 0};  // march trips / cycles by marching lanes: <= 4, <= 8, <= 16, <= 32
+#define VT_T0() (tc0 = clock64())
+#define VT_T1(k) (cyc[k] += clock64() - tc0)
+#else
+#define VT_T0()
+#define VT_T1(k)
 #endif
     bool exhausted = false;                                                  // warp-uniform: the queue is empty
     for (;;) {
@@ -680,6 +715,7 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
 #if VT_TRIPS
             if (COUNT && lane == 0) { trips[3]++; trips[4] += nI; }
 #endif
+            VT_T0();
             if (state == ST_DONE) { finish_ray<FAST, REC>(P, L, fh); L.st = ST_NONE; }
             if (!exhausted) {
                 const unsigned need = __ballot_sync(full, lane_state(L) == ST_NONE);
@@ -693,20 +729,30 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
                 }
                 exhausted = base + (unsigned)cnt >= P.total_rays;
             }
+            VT_T1(0);
         } else if (nH > nM) {
 #if VT_TRIPS
             if (COUNT && lane == 0) { trips[1]++; trips[2] += nH; }
 #endif
+            VT_T0();
             if (state == ST_HIT) shade_one<FAST, REC, COUNT>(P, L, fh, c);
+#if VT_TRIPS
+            __syncwarp(full);
+#endif
+            VT_T1(1);
         } else {
             // ---- march: iterate until too few lanes are still marching -------------------------------------
             const int thr = max(1, (nM * VT_MARCH_KEEP) >> 3);
 #if VT_TRIPS
             if (COUNT && lane == 0) trips[5]++;
+            const long long tm0 = clock64();
 #endif
             for (;;) {
 #if VT_TRIPS
                 if (COUNT && lane == 0) trips[0]++;
+                const int nm_ = __popc(__ballot_sync(full, lane_state(L) == ST_MARCH));
+                const int b_ = nm_ <= 4 ? 0 : nm_ <= 8 ? 1 : nm_ <= 16 ? 2 : 3;
+                const long long tt0 = clock64();
 #endif
                 int ix = 0, iy = 0, iz = 0, looked = 0;
                 bool leave = false;
@@ -715,11 +761,20 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
                     const unsigned ux = (unsigned)(ix - L.cx), uy = (unsigned)(iy - L.cy), uz = (unsigned)(iz - L.cz);
                     leave = max(ux, max(uy, uz)) >= (unsigned)P.s.chunk_size;
                 }
+                VT_T0();
                 if (leave) looked = march_leave_chunk<FAST, FULL_TAIL, COUNT>(P, L, c, ix, iy, iz);
                 __syncwarp(full);
+                VT_T1(3);
                 if (lane_state(L) == ST_MARCH) march_cell<FAST, COUNT>(P, L, c, ix, iy, iz, looked);
+#if VT_TRIPS
+                __syncwarp(full);
+                bk[b_]++; bk[4 + b_] += clock64() - tt0;
+#endif
                 if (__popc(__ballot_sync(full, lane_state(L) == ST_MARCH)) < thr) break;
             }
+#if VT_TRIPS
+            cyc[2] += clock64() - tm0;
+#endif
         }
     }
     if (COUNT && P.counters) {
@@ -730,7 +785,11 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
             if (lane == 0 && t) atomicAdd(P.counters + k, (unsigned long long)t);
         }
 #if VT_TRIPS
-        if (lane == 0) for (int k = 0; k < 6; k++) atomicAdd(P.counters + 8 + k, (unsigned long long)trips[k]);
+        if (lane == 0) {
+            for (int k = 0; k < 6; k++) atomicAdd(P.counters + 8 + k, (unsigned long long)trips[k]);
+            for (int k = 0; k < 4; k++) atomicAdd(P.counters + 14 + k, (unsigned long long)cyc[k]);
+            for (int k = 0; k < 8; k++) atomicAdd(P.counters + 18 + k, (unsigned long long)bk[k]);
+        }
 #endif
     }
     // The last warp to leave resets the queue for the next launch and, with a frame target, publishes the arrival

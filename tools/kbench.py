@@ -56,7 +56,16 @@ def run_variant(spec, frames=8, settings=None, workload=None):
             cn = o2["counters"].cpu().numpy().astype(float)
             print("   pose counters per ray: samples_in %.2f void %.2f hits %.3f probes %.2f rechunk %.2f rays %d" %
                   (cn[1] / cn[0], cn[2] / cn[0], cn[3] / cn[0], cn[4] / cn[0], cn[5] / cn[0], int(cn[0])), flush=True)
-            cn = np.concatenate([cn, o2["trips"].cpu().numpy().astype(float), [0, 0]])
+            tr = o2["trips"].cpu().numpy().astype(float)
+            cn = np.concatenate([cn, tr[:6], [0, 0]])
+            if tr[6:10].sum() > 0:                      # cycles per warp phase (VT_TRIPS build)
+                tot = tr[6] + tr[7] + tr[8]
+                print("   warp cycles: refill %.1f %%  shade %.1f %%  march %.1f %% (of which chunk re-evaluation block %.1f %%)" %
+                      (100 * tr[6] / tot, 100 * tr[7] / tot, 100 * tr[8] / tot, 100 * tr[9] / tot), flush=True)
+                b = tr[10:18]
+                print("   march trips by marching lanes <=4 / <=8 / <=16 / <=32: %s %% of trips, %s %% of march cycles" % (
+                    " / ".join("%.0f" % (100 * v / max(1, b[:4].sum())) for v in b[:4]),
+                    " / ".join("%.0f" % (100 * v / max(1, b[4:].sum())) for v in b[4:])), flush=True)
             if cn[8] > 0:                                # VT_TRIPS build: phase trips per 32 rays and lanes per trip
                 k = cn[0] / 32.0
                 print("   trips per 32 rays: march %.1f (lanes %.1f, %.1f phases) shade %.2f (lanes %.1f) refill %.2f (lanes %.1f)" %
