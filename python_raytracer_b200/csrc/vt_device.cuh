@@ -105,7 +105,12 @@ struct DevParams {
 
 __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
                                               uint32_t k1, uint32_t out[4]) {
-#pragma unroll
+#ifndef VT_PHILOX_UNROLL
+#define VT_PHILOX_UNROLL 10
+#endif
+#define VT_STR2(x) #x
+#define VT_STR(x) VT_STR2(x)
+    _Pragma(VT_STR(unroll VT_PHILOX_UNROLL))
     for (int r = 0; r < 10; r++) {
         uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
         uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
