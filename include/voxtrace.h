@@ -127,6 +127,20 @@ int vt_build_world(vt_ctx *ctx, const vt_object *host_objects, int n, uint8_t *d
  * objects that moved.  Three small launches and one host round trip, independent of the world size. */
 int vt_update_region(vt_ctx *ctx, const vt_object *host_objects, int n, uint8_t *dev_cells, const int32_t lo[3], const int32_t hi[3]);
 
+/* ---- physics: the voxel slice test of Object.update_physics (data.py:520-542) -------------------------------------
+ * Physical fields of a Material (mods/default/init.py:6-17): rows for ids 0..n, row 0 unused. */
+typedef struct { double solidity, friction, elasticity, reserved; } vt_phys_material;
+int vt_set_phys_materials(vt_ctx *ctx, const vt_phys_material *host_materials, int n);
+/* One moving object against one other object whose box touches the slice the mover would enter.  lo / hi: the
+ * inclusive corners post6 of that one-cell-thick slice (data.py:506-517); vel_dir: the unit axis step.  For every cell of
+ * the slice in the reference's order (x, then y, then z): other's voxel at the cell, the mover's voxel at cell - vel_dir
+ * (both through Sprite.pos_rotated); where both exist and pass `solidity > random.random()` the move is blocked and
+ * friction += of * sf * friction_scale, elasticity += oe * se * friction_scale (data.py:540-541) are added to
+ * inout_sums[0..1] in that order -- the sums a caller carries from object to object like the reference's loop.
+ * Solidity 0 and 1 are exact; fractional solidity draws from a Philox stream keyed by (seed, cell).  Synchronises. */
+int vt_slice_collide(vt_ctx *ctx, const vt_object *self, const vt_object *other, const int32_t lo[3], const int32_t hi[3],
+                     const int32_t vel_dir[3], double friction_scale, uint64_t seed, double inout_sums[2], int32_t *out_blocked);
+
 /* Goxel text model -> voxel list, the parser rules of Sprite.load (data.py:271-289): single-space separated
  * "x y z rrggbb" lines, non-numeric lines skipped, colours looked up in `keys` (n_keys strings; unknown ones are
  * dropped), position (size_x - x, z, y).  Returns malloc'ed arrays in FILE ORDER (later entries override earlier

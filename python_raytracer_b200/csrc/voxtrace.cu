@@ -75,6 +75,7 @@ struct vt_ctx {
     long long pool_cap = 0, pool_used = 0;      // in bricks
     std::vector<uint32_t> free_slots;
     double *d_mats = nullptr;                   // [256][8]
+    vt_phys_material *d_phys = nullptr; double *d_phys_out = nullptr;     // physics slice test: material table, result
 
     // persistent kernel state: per-pixel accumulators (zero between launches), ray queue, launch geometry
     unsigned long long *d_acc = nullptr; long long acc_cap = 0;     // in u64 words
@@ -185,6 +186,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     if (ctx->d_wait_status) cudaFreeHost(ctx->d_wait_status);
     for (int k = 0; k < 4; k++) cudaFree(ctx->fx_buf[k]);
     for (int k = 0; k < 3; k++) cudaFree(ctx->scene_buf[k]);
+    cudaFree(ctx->d_phys); cudaFree(ctx->d_phys_out);
     if (ctx->h_word) cudaFreeHost(ctx->h_word);
     for (int k = 0; k < VT_STAGES; k++) { if (ctx->stage[k].h) cudaFreeHost(ctx->stage[k].h); if (ctx->stage[k].ev) cudaEventDestroy(ctx->stage[k].ev); }
     cudaFree(ctx->d_fx_sums); cudaFree(ctx->d_fx_avg); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
@@ -1031,6 +1033,58 @@ extern "C" int vt_trace_rays(vt_ctx *ctx, const double *dev_dirs, const double *
     r.stripe_rows = 1; r.stripe_count = 1;
     TraceArgs t = {dev_dirs, dev_sincos, dev_records, (long long)n};
     return render_impl(ctx, &r, nullptr, nullptr, nullptr, dev_visited, dev_counters, frame_seed, &t);
+}
+
+// ---- physics slice test (vt_physics.cuh) ---------------------------------------------------------------------
+#include "vt_physics.cuh"
+
+extern "C" int vt_set_phys_materials(vt_ctx *ctx, const vt_phys_material *hm, int n) {
+    if (!ctx || !hm) return 1;
+    if (n < 0 || n > VT_MAX_MATERIALS) return fail(ctx, "vt_set_phys_materials: at most 255 materials (id 0 is empty)");
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (!ctx->d_phys) VT_CHECK(ctx, cudaMalloc(&ctx->d_phys, 256 * sizeof(vt_phys_material)));
+    return staged_upload(ctx, ctx->d_phys, hm, (size_t)(n + 1) * sizeof(vt_phys_material));
+}
+
+extern "C" int vt_slice_collide(vt_ctx *ctx, const vt_object *self, const vt_object *other, const int32_t lo[3], const int32_t hi[3],
+                                const int32_t vel_dir[3], double friction_scale, uint64_t seed, double inout_sums[2], int32_t *out_blocked) {
+    if (!ctx || !self || !other || !lo || !hi || !vel_dir || !inout_sums || !out_blocked) return 1;
+    if (!ctx->d_phys) return fail(ctx, "vt_slice_collide: no physical material table (vt_set_phys_materials)");
+    vtphys::SliceArgs a;
+    memset(&a, 0, sizeof a);
+    a.self = *self; a.other = *other;
+    long long n_cells = 1;
+    for (int k = 0; k < 3; k++) {
+        if (hi[k] < lo[k]) { *out_blocked = 0; return 0; }
+        a.lo[k] = lo[k]; a.n[k] = hi[k] - lo[k] + 1; a.dir[k] = vel_dir[k];
+        n_cells *= a.n[k];
+    }
+    if (n_cells > (1LL << 31)) return fail(ctx, "vt_slice_collide: slice too large");
+    const vt_object *both[2] = {self, other};
+    if (int rc = check_objects(ctx, both[0], 1, "vt_slice_collide")) return rc;
+    if (int rc = check_objects(ctx, both[1], 1, "vt_slice_collide")) return rc;
+    a.scale = friction_scale; a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    void *p1 = nullptr, *p2 = nullptr;
+    if (int rc = scene_scratch(ctx, 1, (size_t)n_cells + 64, &p1)) return rc;
+    if (int rc = scene_scratch(ctx, 2, (size_t)n_cells * sizeof(double2) + 64, &p2)) return rc;
+    if (!ctx->h_word) VT_CHECK(ctx, cudaMallocHost(&ctx->h_word, 64));
+    if (!ctx->d_phys_out) VT_CHECK(ctx, cudaMalloc(&ctx->d_phys_out, 4 * sizeof(double)));
+    double *h = reinterpret_cast<double *>(ctx->h_word);
+    h[0] = inout_sums[0]; h[1] = inout_sums[1]; h[2] = 0.0;
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_phys_out, h, 3 * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
+    long long want = (n_cells + 255) / 256;
+    const int grid = (int)(want < (long long)sms * 8 ? want : (long long)sms * 8);
+    vtphys::slice_cells_kernel<<<grid, 256, 0, ctx->stream>>>(a, reinterpret_cast<const double *>(ctx->d_phys), n_cells, static_cast<uint8_t *>(p1), static_cast<double2 *>(p2));
+    vtphys::slice_sum_kernel<<<1, 32, 0, ctx->stream>>>(static_cast<const uint8_t *>(p1), static_cast<const double2 *>(p2), n_cells, ctx->d_phys_out);
+    ctx->launches += 2;
+    VT_CHECK(ctx, cudaGetLastError());
+    VT_CHECK(ctx, cudaMemcpyAsync(h, ctx->d_phys_out, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));
+    VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
+    inout_sums[0] = h[0]; inout_sums[1] = h[1];
+    *out_blocked = h[2] != 0.0 ? 1 : 0;
+    return 0;
 }
 
 // ---- post-FX (vt_postfx.cuh) ------------------------------------------------------------------------------
