@@ -131,6 +131,18 @@ int vt_update_region(vt_ctx *ctx, const vt_object *host_objects, int n, uint8_t 
  * Physical fields of a Material (mods/default/init.py:6-17): rows for ids 0..n, row 0 unused. */
 typedef struct { double solidity, friction, elasticity, reserved; } vt_phys_material;
 int vt_set_phys_materials(vt_ctx *ctx, const vt_phys_material *host_materials, int n);
+/* An object as the physics step sees it: the voxel dictionary of its sprite's active frame as a dense grid of material ids
+ * over the bounding box of the dictionary's keys (keys may lie outside [0, size): Sprite.load maps file column x = 0 to
+ * x = size.x, data.py:285), Sprite.size, Object.mins (data.py:480-484) and the 90-degree rotation steps. */
+typedef struct {
+    const uint8_t *dev_grid;       /* [grid_dims0][grid_dims1][grid_dims2] u8, z fastest; 0 = no voxel */
+    int32_t grid_lo[3];            /* sprite-local coordinate of grid[0][0][0] */
+    int32_t grid_dims[3];
+    int32_t size[3];               /* Sprite.size */
+    int32_t mins[3];               /* Object.mins */
+    int32_t angle[3];              /* round(rot / 90) % 4 per axis */
+    int32_t reserved;
+} vt_phys_object;
 /* One moving object against one other object whose box touches the slice the mover would enter.  lo / hi: the
  * inclusive corners post6 of that one-cell-thick slice (data.py:506-517); vel_dir: the unit axis step.  For every cell of
  * the slice in the reference's order (x, then y, then z): other's voxel at the cell, the mover's voxel at cell - vel_dir
@@ -138,7 +150,7 @@ int vt_set_phys_materials(vt_ctx *ctx, const vt_phys_material *host_materials, i
  * friction += of * sf * friction_scale, elasticity += oe * se * friction_scale (data.py:540-541) are added to
  * inout_sums[0..1] in that order -- the sums a caller carries from object to object like the reference's loop.
  * Solidity 0 and 1 are exact; fractional solidity draws from a Philox stream keyed by (seed, cell).  Synchronises. */
-int vt_slice_collide(vt_ctx *ctx, const vt_object *self, const vt_object *other, const int32_t lo[3], const int32_t hi[3],
+int vt_slice_collide(vt_ctx *ctx, const vt_phys_object *self, const vt_phys_object *other, const int32_t lo[3], const int32_t hi[3],
                      const int32_t vel_dir[3], double friction_scale, uint64_t seed, double inout_sums[2], int32_t *out_blocked);
 
 /* Goxel text model -> voxel list, the parser rules of Sprite.load (data.py:271-289): single-space separated

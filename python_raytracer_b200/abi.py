@@ -41,6 +41,11 @@ class VtObject(C.Structure):
                 ("angle", C.c_int32 * 3), ("reserved", C.c_int32)]
 
 
+class VtPhysObject(C.Structure):
+    _fields_ = [("dev_grid", C.c_void_p), ("grid_lo", C.c_int32 * 3), ("grid_dims", C.c_int32 * 3), ("size", C.c_int32 * 3),
+                ("mins", C.c_int32 * 3), ("angle", C.c_int32 * 3), ("reserved", C.c_int32)]
+
+
 class VtFx(C.Structure):
     _fields_ = [("width", C.c_int32), ("height", C.c_int32), ("out_width", C.c_int32), ("out_height", C.c_int32),
                 ("iris_on", C.c_int32), ("reserved", C.c_int32), ("spill", C.c_double), ("iris", C.c_double),
@@ -107,7 +112,7 @@ def load(path: str | None = None):
         "vt_wait_status_peek": (C.c_int, [vp, C.POINTER(C.c_int)]),
         "vt_copy_to_host": (C.c_int, [vp, vp, vp, i64]),
         "vt_set_phys_materials": (C.c_int, [vp, vp, i32]),
-        "vt_slice_collide": (C.c_int, [vp, C.POINTER(VtObject), C.POINTER(VtObject), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+        "vt_slice_collide": (C.c_int, [vp, C.POINTER(VtPhysObject), C.POINTER(VtPhysObject), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                        C.POINTER(C.c_int32), C.c_double, u64, C.POINTER(C.c_double), C.POINTER(C.c_int32)]),
         "vt_set_tuning": (C.c_int, [vp, C.c_char_p, i32]),
         "vt_clear_world": (C.c_int, [vp]),

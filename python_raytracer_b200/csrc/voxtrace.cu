@@ -1046,7 +1046,7 @@ extern "C" int vt_set_phys_materials(vt_ctx *ctx, const vt_phys_material *hm, in
     return staged_upload(ctx, ctx->d_phys, hm, (size_t)(n + 1) * sizeof(vt_phys_material));
 }
 
-extern "C" int vt_slice_collide(vt_ctx *ctx, const vt_object *self, const vt_object *other, const int32_t lo[3], const int32_t hi[3],
+extern "C" int vt_slice_collide(vt_ctx *ctx, const vt_phys_object *self, const vt_phys_object *other, const int32_t lo[3], const int32_t hi[3],
                                 const int32_t vel_dir[3], double friction_scale, uint64_t seed, double inout_sums[2], int32_t *out_blocked) {
     if (!ctx || !self || !other || !lo || !hi || !vel_dir || !inout_sums || !out_blocked) return 1;
     if (!ctx->d_phys) return fail(ctx, "vt_slice_collide: no physical material table (vt_set_phys_materials)");
@@ -1060,9 +1060,14 @@ extern "C" int vt_slice_collide(vt_ctx *ctx, const vt_object *self, const vt_obj
         n_cells *= a.n[k];
     }
     if (n_cells > (1LL << 31)) return fail(ctx, "vt_slice_collide: slice too large");
-    const vt_object *both[2] = {self, other};
-    if (int rc = check_objects(ctx, both[0], 1, "vt_slice_collide")) return rc;
-    if (int rc = check_objects(ctx, both[1], 1, "vt_slice_collide")) return rc;
+    const vt_phys_object *both[2] = {self, other};
+    for (int k = 0; k < 2; k++) {
+        if (!both[k]->dev_grid) return fail(ctx, "vt_slice_collide: object without a voxel grid");
+        for (int a2 = 0; a2 < 3; a2++) {
+            if (both[k]->size[a2] <= 0 || both[k]->grid_dims[a2] <= 0) return fail(ctx, "vt_slice_collide: sprite size / grid dims must be positive");
+            if (both[k]->angle[a2] < 0 || both[k]->angle[a2] > 3) return fail(ctx, "vt_slice_collide: angle must be 0..3");
+        }
+    }
     a.scale = friction_scale; a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
     void *p1 = nullptr, *p2 = nullptr;

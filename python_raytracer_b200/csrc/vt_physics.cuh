@@ -15,19 +15,25 @@
 namespace vtphys {
 
 struct SliceArgs {
-    vt_object self, other;
+    vt_phys_object self, other;
     int lo[3], n[3];                 // slice corner and cells per axis (post6 is inclusive at both ends, data.py:533-535)
     int dir[3];                      // vel_dir, one of the six axis directions
     double scale;                    // settings.friction (data.py:540-541)
     uint32_t seed_lo, seed_hi;
 };
 
-// Sprite.get_voxel(None, pos - obj.mins, obj.rot) (data.py:417-419): material id or 0
-__device__ __forceinline__ int sprite_voxel(const vt_object &o, int x, int y, int z) {
+// Sprite.get_voxel(None, pos - obj.mins, obj.rot) (data.py:417-419): material id or 0.  The voxel dictionary of a sprite
+// may hold keys outside [0, size) -- Sprite.load maps file column x = 0 to x = size.x (data.py:285), which the renderer
+// never draws but this test does ask for -- so the grid covers the keys' bounding box [grid_lo, grid_lo + grid_dims).
+__device__ __forceinline__ int sprite_voxel(const vt_phys_object &o, int x, int y, int z) {
     x -= o.mins[0]; y -= o.mins[1]; z -= o.mins[2];
-    vt::pos_rotated(o, x, y, z);
-    if ((unsigned)x >= (unsigned)o.size[0] || (unsigned)y >= (unsigned)o.size[1] || (unsigned)z >= (unsigned)o.size[2]) return 0;
-    return __ldg(o.dev_sprite + ((size_t)x * o.size[1] + y) * o.size[2] + z);
+    vt_object r;                                           // pos_rotated reads size and angle only
+    r.size[0] = o.size[0]; r.size[1] = o.size[1]; r.size[2] = o.size[2];
+    r.angle[0] = o.angle[0]; r.angle[1] = o.angle[1]; r.angle[2] = o.angle[2];
+    vt::pos_rotated(r, x, y, z);
+    x -= o.grid_lo[0]; y -= o.grid_lo[1]; z -= o.grid_lo[2];
+    if ((unsigned)x >= (unsigned)o.grid_dims[0] || (unsigned)y >= (unsigned)o.grid_dims[1] || (unsigned)z >= (unsigned)o.grid_dims[2]) return 0;
+    return __ldg(o.dev_grid + ((size_t)x * o.grid_dims[1] + y) * o.grid_dims[2] + z);
 }
 
 __device__ __forceinline__ bool solid(double solidity, uint32_t cell, uint32_t which, uint32_t seed_lo, uint32_t seed_hi) {
