@@ -1082,7 +1082,7 @@ extern "C" int vt_slice_collide(vt_ctx *ctx, const vt_phys_object *self, const v
     long long want = (n_cells + 255) / 256;
     const int grid = (int)(want < (long long)sms * 8 ? want : (long long)sms * 8);
     vtphys::slice_cells_kernel<<<grid, 256, 0, ctx->stream>>>(a, reinterpret_cast<const double *>(ctx->d_phys), n_cells, static_cast<uint8_t *>(p1), static_cast<double2 *>(p2));
-    vtphys::slice_sum_kernel<<<1, 32, 0, ctx->stream>>>(static_cast<const uint8_t *>(p1), static_cast<const double2 *>(p2), n_cells, ctx->d_phys_out);
+    vtphys::slice_sum_kernel<<<1, 1024, 0, ctx->stream>>>(static_cast<const uint8_t *>(p1), static_cast<double2 *>(p2), n_cells, ctx->d_phys_out);
     ctx->launches += 2;
     VT_CHECK(ctx, cudaGetLastError());
     VT_CHECK(ctx, cudaMemcpyAsync(h, ctx->d_phys_out, 3 * sizeof(double), cudaMemcpyDeviceToHost, ctx->stream));

@@ -67,26 +67,36 @@ __global__ void slice_cells_kernel(const SliceArgs a, const double *__restrict__
     }
 }
 
-// One warp adds the contributions in cell order: out = {friction, elasticity, blocked} continues from the sums passed in.
-__global__ void slice_sum_kernel(const uint8_t *__restrict__ flag, const double2 *__restrict__ contrib, long long n_cells, double *__restrict__ out) {
+// The contributions are added in cell order (fp64 sums are order-sensitive and the reference's order is x, y, z): one
+// block first compacts the flagged cells in place, in order (ballot + prefix over the 32 warps, 1024 cells per round),
+// then thread 0 adds the compacted list sequentially; out = {friction, elasticity, blocked} continues from the sums passed
+// in.  Contact surfaces are small next to the slice, so the sequential part is short.
+__global__ void __launch_bounds__(1024) slice_sum_kernel(const uint8_t *__restrict__ flag, double2 *__restrict__ contrib, long long n_cells, double *__restrict__ out) {
+    __shared__ int warp_cnt[32];
+    __shared__ long long total;
     const unsigned full = 0xffffffffu;
-    const int lane = threadIdx.x;
-    double fr = out[0], el = out[1];
-    bool blocked = false;
-    for (long long base = 0; base < n_cells; base += 32) {
-        const long long i = base + lane;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) total = 0;
+    __syncthreads();
+    for (long long base = 0; base < n_cells; base += 1024) {
+        const long long i = base + threadIdx.x;
         const bool f = i < n_cells && flag[i];
         const double2 c = f ? contrib[i] : make_double2(0.0, 0.0);
-        unsigned m = __ballot_sync(full, f);
-        while (m) {
-            const int j = __ffs(m) - 1;
-            fr += __shfl_sync(full, c.x, j);
-            el += __shfl_sync(full, c.y, j);
-            blocked = true;
-            m &= m - 1u;
-        }
+        const unsigned m = __ballot_sync(full, f);
+        if (lane == 0) warp_cnt[warp] = __popc(m);
+        __syncthreads();                                    // every entry of this round is in registers: in-place writes are safe
+        int before = 0, all = 0;
+        for (int w = 0; w < 32; w++) { const int k = warp_cnt[w]; all += k; if (w < warp) before += k; }
+        if (f) contrib[total + before + __popc(m & ((1u << lane) - 1u))] = c;
+        __syncthreads();
+        if (threadIdx.x == 0) total += all;
+        __syncthreads();
     }
-    if (lane == 0) { out[0] = fr; out[1] = el; out[2] = blocked ? 1.0 : 0.0; }
+    if (threadIdx.x == 0) {
+        double fr = out[0], el = out[1];
+        for (long long k = 0; k < total; k++) { fr += contrib[k].x; el += contrib[k].y; }
+        out[0] = fr; out[1] = el; out[2] = total > 0 ? 1.0 : 0.0;
+    }
 }
 
 }  // namespace vtphys
