@@ -2,11 +2,12 @@
 // lib.material / material_background (lib.py:448-476) and Frame.get_voxel (data.py:136-145) for a whole frame.
 // Every ray produces the reference's sample positions, hits and colours; what is specific to the GPU is the schedule:
 //
-//   * One persistent grid per frame.  Every LANE owns one ray at a time and fetches the next ray slot from a
-//     global queue when its ray ends (rays of a frame differ in length by 10x, so a warp that waits for its
-//     longest ray idles most lanes).  Pixel means are accumulated with one 64-bit atomic per ray: the channel
-//     sums are sums of integers 0..255, so the order of arrival cannot change the result; the sample that
-//     completes a pixel writes it and clears the accumulator.
+//   * One persistent grid per frame.  Every lane owns one ray at a time; a warp draws a PACKET of 32 ray slots (one
+//     sample index of an 8 x 4 pixel tile) from a global queue when all its rays have ended.  (Refilling single lanes
+//     as their rays end is implemented -- `refill_min` < 32 -- and measured slower: young primary rays mixed with
+//     bounced ones march with fewer lanes per trip)  Pixel means are accumulated with one 64-bit
+//     atomic per ray: the channel sums are sums of integers 0..255, so the order of arrival cannot change the result;
+//     the sample that completes a pixel writes it and clears the accumulator.
 //   * A warp is a small state machine.  Lanes are MARCH (stepping through cells), HIT (found a solid cell,
 //     material interaction pending) or idle (ray ended / no ray).  Each round the warp runs the phase most lanes
 //     wait for, so the expensive rare work (pow, divisions, Philox, sincos, atomics) runs with many lanes active
@@ -22,12 +23,6 @@
 #endif
 #ifndef VT_TRIPS           // dev instrumentation (tools/kbench.py KB_COUNTERS): phase trip counts in counters[8..13]
 #define VT_TRIPS 0
-#endif
-#ifndef VT_LODLOOP
-#define VT_LODLOOP 0                 // per-lane loop inside LOD chunks: measured, no gain (C4 +1 %, bench +0.3 %), off
-#endif
-#ifndef VT_LOOP2
-#define VT_LOOP2 1                   // brick-local loop in two specialised copies (empty / non-empty brick)
 #endif
 #ifndef VT_SINCOS_SMALL
 #define VT_SINCOS_SMALL 1            // sin / cos of the half lens angles without argument reduction when |a| <= pi/4
@@ -343,7 +338,6 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
                 // The world origin is a multiple of 8 here, so brick membership is tested on absolute cells.
                 if (L.res == 1 && P.brick_runs && VT_IN(b <= w.pool_slots, 5)) {
                     const int ax = ix + w.ox, ay = iy + w.oy, az = iz + w.oz;
-#if VT_LOOP2
                     // Two specialised loops.  Empty brick: nothing to load, the loop is the position update, the
                     // life test, three floors and the same-brick test.  Non-empty brick: the cell index is taken
                     // relative to the brick's corner -- jx * 64 + jy * 8 + jz minus the same expression of the corner,
@@ -371,19 +365,6 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
                         if (COUNT) c.in_chunk++;
                         mat = __ldg(pb + ((((uint32_t)jx << 6) + ((uint32_t)jy << 3) + (uint32_t)jz) - corner));
                     }
-#else
-                    const uint8_t *pb = w.pool + (size_t)(b ? b - 1u : 0u) * 512u;
-                    if (b) mat = __ldg(pb + (((ix & 7) << 6) | ((iy & 7) << 3) | (iz & 7)));
-                    while (!mat) {
-                        L.step += 1.0;
-                        L.px += L.vx; L.py += L.vy; L.pz += L.vz;       // vel * 1.0 == vel
-                        if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
-                        const int jx = floor_i(L.px), jy = floor_i(L.py), jz = floor_i(L.pz);
-                        if ((((jx ^ ax) | (jy ^ ay) | (jz ^ az)) & ~7) != 0) return;      // next sample: another brick
-                        if (COUNT) c.in_chunk++;
-                        if (b) mat = __ldg(pb + (((jx & 7) << 6) | ((jy & 7) << 3) | (jz & 7)));
-                    }
-#endif
                 } else if (b && VT_IN(b <= w.pool_slots, 5))
                     mat = __ldg(&w.pool[(size_t)(b - 1u) * 512u + (((qx & 7) << 6) | ((qy & 7) << 3) | (qz & 7))]);
             }
@@ -395,28 +376,7 @@ __device__ __forceinline__ void march_cell(const DevParams &P, Lane &L, Counters
             if (!(L.step < L.life)) lane_set_state(L, ST_DONE);
             return;
         }
-#if VT_LODLOOP
-        // LOD chunk: keep stepping by `resolution` while the samples stay strictly inside this chunk's box
-        {
-            const unsigned cs = (unsigned)P.s.chunk_size;
-            const double dr = i2d(L.res);
-            for (;;) {
-                L.step += dr;
-                L.px += L.vx * dr; L.py += L.vy * dr; L.pz += L.vz * dr;
-                if (!(L.step < L.life)) { lane_set_state(L, ST_DONE); return; }
-                const int jx = floor_i(L.px) - w.ox, jy = floor_i(L.py) - w.oy, jz = floor_i(L.pz) - w.oz;
-                if (max((unsigned)(jx - L.cx), max((unsigned)(jy - L.cy), (unsigned)(jz - L.cz))) >= cs) return;
-                if (COUNT) c.in_chunk++;
-                const int qx = lod_snap<FAST>(P, L.res, jx, 0), qy = lod_snap<FAST>(P, L.res, jy, 1), qz = lod_snap<FAST>(P, L.res, jz, 2);
-                if (qx >= L.cx && qy >= L.cy && qz >= L.cz) {
-                    const int m2 = cell_at(w, qx, qy, qz);
-                    if (m2) { L.st = (L.st & ~0xfffu) | ST_HIT | ((uint32_t)m2 << 2); return; }
-                }
-            }
-        }
-#else
         advance(L, i2d(L.res));
-#endif
     } else {
         if (COUNT) c.in_void++;
         advance(L, void_step2<FAST>(L.px, L.py, L.pz, P.s.chunk_radius, P.s.chunk_size, P.cs_shift));
