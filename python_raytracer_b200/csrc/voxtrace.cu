@@ -58,6 +58,7 @@ struct vt_ctx {
     // lens tables (dof == 0): rebuilt when (lens, width, height, proportions) change
     double *d_col_sc = nullptr, *d_row_sc = nullptr;
     double *d_dir_x = nullptr, *d_dir_y = nullptr; int dir_w = 0, dir_h = 0;   // init.py:131-132 per column / row
+    double *d_lens_x = nullptr, *d_lens_y = nullptr; double dir_lens = -1, dir_prop = -1;   // init.py:41-42 without the jitter
     int tab_w = 0, tab_h = 0; double tab_lens = -1, tab_prop = -1;
 
     // world
@@ -190,6 +191,7 @@ extern "C" void vt_destroy(vt_ctx *ctx) {
     if (ctx->h_word) cudaFreeHost(ctx->h_word);
     for (int k = 0; k < VT_STAGES; k++) { if (ctx->stage[k].h) cudaFreeHost(ctx->stage[k].h); if (ctx->stage[k].ev) cudaEventDestroy(ctx->stage[k].ev); }
     cudaFree(ctx->d_fx_sums); cudaFree(ctx->d_fx_avg); cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y);
+    cudaFree(ctx->d_lens_x); cudaFree(ctx->d_lens_y);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -798,18 +800,23 @@ static int update_lens_tables(vt_ctx *ctx) {
 // dir_x / dir_y of init.py:131-132 for every column / row: a correctly rounded division each, done once on the host
 static int update_dir_tables(vt_ctx *ctx) {
     const vt_settings &s = ctx->s;
-    if (ctx->d_dir_x && ctx->dir_w == s.width && ctx->dir_h == s.height) return 0;
+    if (ctx->d_dir_x && ctx->dir_w == s.width && ctx->dir_h == s.height && ctx->dir_lens == ctx->cam_lens && ctx->dir_prop == s.proportions) return 0;
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y); ctx->d_dir_x = ctx->d_dir_y = nullptr;
-    std::vector<double> dx((size_t)s.width), dy((size_t)s.height);
-    for (int x = 0; x < s.width; x++) dx[x] = -1.0 + ((double)x / (double)s.width) * 2.0;
-    for (int y = 0; y < s.height; y++) dy[y] = -1.0 + ((double)y / (double)s.height) * 2.0;
+    cudaFree(ctx->d_dir_x); cudaFree(ctx->d_dir_y); cudaFree(ctx->d_lens_x); cudaFree(ctx->d_lens_y);
+    ctx->d_dir_x = ctx->d_dir_y = ctx->d_lens_x = ctx->d_lens_y = nullptr;
+    std::vector<double> dx((size_t)s.width), dy((size_t)s.height), lx((size_t)s.width), ly((size_t)s.height);
+    for (int x = 0; x < s.width; x++) { dx[x] = -1.0 + ((double)x / (double)s.width) * 2.0; lx[x] = (dx[x] / s.proportions) * ctx->cam_lens; }
+    for (int y = 0; y < s.height; y++) { dy[y] = -1.0 + ((double)y / (double)s.height) * 2.0; ly[y] = (dy[y] * s.proportions) * ctx->cam_lens; }
     VT_CHECK(ctx, cudaMalloc(&ctx->d_dir_x, dx.size() * sizeof(double)));
     VT_CHECK(ctx, cudaMalloc(&ctx->d_dir_y, dy.size() * sizeof(double)));
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_lens_x, lx.size() * sizeof(double)));
+    VT_CHECK(ctx, cudaMalloc(&ctx->d_lens_y, ly.size() * sizeof(double)));
     VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_dir_x, dx.data(), dx.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_dir_y, dy.data(), dy.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_lens_x, lx.data(), lx.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
+    VT_CHECK(ctx, cudaMemcpyAsync(ctx->d_lens_y, ly.data(), ly.size() * sizeof(double), cudaMemcpyHostToDevice, ctx->stream));
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
-    ctx->dir_w = s.width; ctx->dir_h = s.height;
+    ctx->dir_w = s.width; ctx->dir_h = s.height; ctx->dir_lens = ctx->cam_lens; ctx->dir_prop = s.proportions;
     return 0;
 }
 
@@ -945,7 +952,7 @@ static int render_impl(vt_ctx *ctx, const vt_region *region, uint8_t *dev_rgba8,
     memcpy(P.cam.rot, ctx->cam_rot, sizeof P.cam.rot);
     P.cam.lens = ctx->cam_lens;
     if (int rc = update_dir_tables(ctx)) return rc;
-    P.cam.dir_x = ctx->d_dir_x; P.cam.dir_y = ctx->d_dir_y;
+    P.cam.dir_x = ctx->d_dir_x; P.cam.dir_y = ctx->d_dir_y; P.cam.lens_x = ctx->d_lens_x; P.cam.lens_y = ctx->d_lens_y;
     if (s.dof == 0.0 && !trace) {
         if (int rc = update_lens_tables(ctx)) return rc;
         P.cam.col_sc = ctx->d_col_sc; P.cam.row_sc = ctx->d_row_sc;

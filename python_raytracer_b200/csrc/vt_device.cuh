@@ -52,6 +52,8 @@ struct DevCamera {
     const double *row_sc;           // [height][2] sin, cos of the row's half pitch   (dof == 0 only)
     const double *dir_x;            // [width]  -1 + (x / width) * 2   (init.py:131), host division
     const double *dir_y;            // [height] -1 + (y / height) * 2  (init.py:132)
+    const double *lens_x;           // [width]  (dir_x / proportions) * lens  (init.py:41), host arithmetic
+    const double *lens_y;           // [height] (dir_y * proportions) * lens  (init.py:42)
 };
 
 struct DevParams {

@@ -34,7 +34,7 @@
 #define VT_COLD_SMEM 1               // per-ray state the march loops never touch lives in shared memory, not in registers
 #endif
 #ifndef VT_MINB
-#define VT_MINB 12                   // resident 128-thread blocks per SM the register budget is sized for
+#define VT_MINB 10                   // resident 128-thread blocks per SM the register budget is sized for (48 registers)
 #endif
 
 namespace vt {
@@ -58,7 +58,7 @@ __device__ __forceinline__ double pmax(double a, double b) { return b > a ? b : 
 struct ColdStore {
     double bounces[128], energy[128];
     int col[128];
-    uint32_t xy[128], out_i[128], draw[128], w2[128], w3[128];
+    uint32_t xy[128], out_i[128], draw[128], w2[128], w3[128], nsmp[128];
 };
 struct Lane {
     double px, py, pz, vx, vy, vz, step, life;
@@ -71,12 +71,14 @@ struct Lane {
     uint32_t &xy;                   // pixel x | y << 16
     uint32_t &out_i;                // output index of the pixel
     uint32_t &draw, &w2, &w3;       // Philox draw counter and the cached second uniform of the last block
+    uint32_t &nsmp;                 // samples traced for the ray's pixel (init.py:134)
     __device__ __forceinline__ Lane(ColdStore &s, int t)
-        : bounces(s.bounces[t]), energy(s.energy[t]), col(s.col[t]), xy(s.xy[t]), out_i(s.out_i[t]), draw(s.draw[t]), w2(s.w2[t]), w3(s.w3[t]) {}
+        : bounces(s.bounces[t]), energy(s.energy[t]), col(s.col[t]), xy(s.xy[t]), out_i(s.out_i[t]), draw(s.draw[t]), w2(s.w2[t]), w3(s.w3[t]),
+          nsmp(s.nsmp[t]) {}
 #else
     double bounces, energy;
     int col;
-    uint32_t xy, out_i, draw, w2, w3;
+    uint32_t xy, out_i, draw, w2, w3, nsmp;
     __device__ __forceinline__ Lane(ColdStore &, int) {}
 #endif
 };
@@ -463,9 +465,9 @@ __device__ __forceinline__ void shade_one(const DevParams &P, Lane &L, FirstHit 
 __device__ __forceinline__ int pixel_samples(const DevParams &P, int x, int y, double &dir_x, double &dir_y, double &detail) {
     const vt_settings &s = P.s;
     if (!VT_IN((unsigned)x < (unsigned)s.width && (unsigned)y < (unsigned)s.height, 7)) { dir_x = dir_y = 0.0; detail = 1.0; return 1; }
+    if (s.lod_edge == 0.0) { dir_x = dir_y = 0.0; detail = 1.0; return s.samples < 1 ? 1 : s.samples; }
     dir_x = __ldg(P.cam.dir_x + x);
     dir_y = __ldg(P.cam.dir_y + y);
-    if (s.lod_edge == 0.0) { detail = 1.0; return s.samples < 1 ? 1 : s.samples; }
     detail = 1.0 - fabs(dir_x * dir_y) * s.lod_edge;
     int n = rint_i(i2d(s.samples) * detail);
     return n < 1 ? 1 : n;
@@ -500,8 +502,7 @@ __device__ __forceinline__ void finish_ray(const DevParams &P, Lane &L, const Fi
     }
     double alpha = rint_d(pmin(1.0, L.energy + s.shutter) * 255.0);            // init.py:141
     const int x = (int)(L.xy & 0xffffu), y = (int)(L.xy >> 16);
-    double dx_, dy_, det_;
-    const int n = pixel_samples(P, x, y, dx_, dy_, det_);
+    const int n = (int)L.nsmp;
     const size_t i = L.out_i;
     if (!VT_IN((long long)i < P.n_pixels, 8)) return;
     if (REC && lane_sample(L) == 0u) {
@@ -600,11 +601,27 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
     rays++;
     L.xy = (uint32_t)x | ((uint32_t)y << 16);
     L.st = ST_MARCH | (sample << 12);
+    L.nsmp = (uint32_t)n;
     L.draw = 0; L.w2 = L.w3 = 0;
     double ray_detail = detail;                                              // trace() takes `detail` as given (init.py:56)
+    double jit_x = 0.0, jit_y = 0.0;                                         // rand(dof), rand(dof) of init.py:41-42
     if (!tracing) {
-        double u = lane_rng_next(P, L);                                      // drawn even when lod_random == 0 (init.py:139)
+        // Draws 0, 1, 2 of the ray's stream: lod_random (drawn even when it is 0, init.py:139), then the two lens jitters
+        // (rand(0) draws nothing, lib.py:431-434).  Written out block by block -- the generic draw-by-draw helper inlined
+        // three times cost 60 instructions more.
+        const uint32_t pix = (uint32_t)y * (uint32_t)s.width + (uint32_t)x;
+        const uint4 w0 = philox_block(0u, sample, P.seed_lo, P.seed_hi, pix);
+        const double u = u53m(w0.x, w0.y);
+        L.draw = 1; L.w2 = w0.z; L.w3 = w0.w;
+        if (s.dof != 0.0) {
+            jit_x = (-1.0 + u53m(w0.z, w0.w) * 2.0) * s.dof;
+            const uint4 w1 = philox_block(1u, sample, P.seed_lo, P.seed_hi, pix);
+            jit_y = (-1.0 + u53m(w1.x, w1.y) * 2.0) * s.dof;
+            L.draw = 3; L.w2 = w1.z; L.w3 = w1.w;
+        }
         ray_detail = detail / (1.0 + u2d(sample) * s.lod_samples) * (1.0 - s.lod_random * u);
+    } else {
+        jit_x = lane_rng_rand(P, L, s.dof); jit_y = lane_rng_rand(P, L, s.dof);
     }
     double sy, cy, sz, cz;
     if (tracing && s.dof == 0.0 && P.dir_sc) {
@@ -615,8 +632,9 @@ __device__ __forceinline__ void start_ray(const DevParams &P, Lane &L, FirstHit 
         sz = __ldg(P.cam.row_sc + 2 * y); cz = __ldg(P.cam.row_sc + 2 * y + 1);
     } else {
         const double deg2rad = 3.14159265358979323846 / 180.0;
-        double lens_x = (dir_x / s.proportions) * P.cam.lens + lane_rng_rand(P, L, s.dof);
-        double lens_y = (dir_y * s.proportions) * P.cam.lens + lane_rng_rand(P, L, s.dof);
+        // (dir_x / proportions) * lens depends on the column only, (dir_y * proportions) * lens on the row only: host tables
+        double lens_x = (tracing ? (dir_x / s.proportions) * P.cam.lens : __ldg(P.cam.lens_x + x)) + jit_x;
+        double lens_y = (tracing ? (dir_y * s.proportions) * P.cam.lens : __ldg(P.cam.lens_y + y)) + jit_y;
         double rad_y = (-lens_x) * deg2rad, rad_z = (+lens_y) * deg2rad;
         double2 scy = sincos_out(rad_y / 2.0), scz = sincos_out(rad_z / 2.0);
         sy = scy.x; cy = scy.y; sz = scz.x; cz = scz.y;
@@ -653,7 +671,7 @@ __global__ void __launch_bounds__(128, VT_MINB) render_persistent(const __grid_c
 #endif
     Lane L(cold, threadIdx.x);
     L.st = ST_NONE; L.px = L.py = L.pz = L.vx = L.vy = L.vz = 0.0; L.step = L.life = L.bounces = L.energy = 0.0;
-    L.col = 0; L.cx = L.cy = L.cz = 0; L.res = 0; L.xy = 0; L.out_i = 0; L.draw = L.w2 = L.w3 = 0;
+    L.col = 0; L.cx = L.cy = L.cz = 0; L.res = 0; L.xy = 0; L.out_i = 0; L.draw = L.w2 = L.w3 = 0; L.nsmp = 1;
     FirstHit fh; fh.hits = fh.fflag = fh.fx = fh.fy = fh.fz = 0; fh.first_step = -1.0;
     Counters c = {0, 0, 0, 0, 0, 0};
     unsigned rays = 0;
