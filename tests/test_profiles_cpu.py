@@ -7,11 +7,16 @@ import sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
-def test_traffic_json_follows_from_the_committed_ncu_summary():
-    tj = json.load(open(os.path.join(ROOT, "profiles", "r1_traffic.json")))
+import pytest
+
+
+@pytest.mark.parametrize("name", ["r1_traffic.json", "r2_traffic.json"])
+def test_traffic_json_follows_from_the_committed_ncu_summary(name):
+    tj = json.load(open(os.path.join(ROOT, "profiles", name)))
     cited = tj["source"].split(" ")[0]
     assert os.path.exists(os.path.join(ROOT, cited)), cited
-    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_traffic_json.py"), os.path.join(ROOT, cited), cited],
+    extra = [tj["kernel_sha256"]] if "kernel_sha256" in tj else []
+    out = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_traffic_json.py"), os.path.join(ROOT, cited), cited] + extra,
                          capture_output=True, text=True, check=True).stdout
     again = json.loads(out)
     assert again == tj
