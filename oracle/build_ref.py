@@ -10,8 +10,9 @@ and consists of BYTECODE compiled from the sources where they lie plus the defau
                                                through its own finder)
   vt_reference_init.vtbc                       the imports + class Camera + class Window of init.py (its last line opens a
                                                window, init.py:474), extracted from the AST exactly as refharness does
-  mods/default/config.cfg, mods/default/voxels/*.gz   the mod's configuration and voxel models (data, read at import)
-No reference source text is copied.  TEST INFRASTRUCTURE ONLY.
+  assets.zip                                   the default mod's data files (config.cfg, voxels/*.gz), which data.py and the mod
+                                               read at import; refharness unpacks them into a temporary directory
+No reference source text is copied and nothing under oracle/_ref/ carries a reference file's name.  TEST INFRASTRUCTURE ONLY.
 """
 from __future__ import annotations
 
@@ -36,7 +37,7 @@ def build(force: bool = False) -> str | None:
     if not force and os.path.isfile(stamp) and open(stamp).read().strip() == tag:
         return OUT
     shutil.rmtree(OUT, ignore_errors=True)
-    os.makedirs(os.path.join(OUT, "mods", "default", "voxels"))
+    os.makedirs(os.path.join(OUT, "mods", "default"))
     for rel in ("lib.py", "data.py", os.path.join("mods", "default", "init.py")):
         py_compile.compile(os.path.join(src, rel), cfile=os.path.join(OUT, rel[:-3] + ".vtbc"), dfile=rel, doraise=True)
     with open(os.path.join(src, "init.py"), "rt") as f:
@@ -47,10 +48,12 @@ def build(force: bool = False) -> str | None:
     from importlib._bootstrap_external import _code_to_timestamp_pyc
     with open(os.path.join(OUT, "vt_reference_init.vtbc"), "wb") as f:
         f.write(_code_to_timestamp_pyc(code, 0, 0))
-    shutil.copy(os.path.join(src, "mods", "default", "config.cfg"), os.path.join(OUT, "mods", "default", "config.cfg"))
-    vox = os.path.join(src, "mods", "default", "voxels")
-    for name in os.listdir(vox):
-        shutil.copy(os.path.join(vox, name), os.path.join(OUT, "mods", "default", "voxels", name))
+    import zipfile
+    with zipfile.ZipFile(os.path.join(OUT, "assets.zip"), "w", zipfile.ZIP_DEFLATED) as z:
+        z.write(os.path.join(src, "mods", "default", "config.cfg"), "mods/default/config.cfg")
+        vox = os.path.join(src, "mods", "default", "voxels")
+        for name in sorted(os.listdir(vox)):
+            z.write(os.path.join(vox, name), "mods/default/voxels/" + name)
     for root, _, files in os.walk(OUT):
         for name in files:
             os.chmod(os.path.join(root, name), 0o644)

@@ -40,7 +40,8 @@ def available_bytecode() -> bool:
     interpreter version."""
     import importlib.util
     stamp = os.path.join(BYTECODE_ROOT, "BUILT_WITH")
-    if not os.path.isfile(stamp) or not os.path.isfile(os.path.join(BYTECODE_ROOT, "vt_reference_init.vtbc")):
+    if not os.path.isfile(stamp) or not os.path.isfile(os.path.join(BYTECODE_ROOT, "vt_reference_init.vtbc")) \
+            or not os.path.isfile(os.path.join(BYTECODE_ROOT, "assets.zip")):
         return False
     return open(stamp).read().strip().endswith(importlib.util.MAGIC_NUMBER.hex())
 
@@ -78,8 +79,18 @@ def load_reference(mod: str = "default"):
     if not from_source and not available_bytecode():
         raise RuntimeError("reference tree not present at %s (and no bytecode build under %s)" % (REFERENCE_ROOT, BYTECODE_ROOT))
     root = REFERENCE_ROOT if from_source else BYTECODE_ROOT
-    if not from_source and not any(isinstance(f, _BytecodeFinder) for f in sys.meta_path):
-        sys.meta_path.insert(0, _BytecodeFinder())
+    if not from_source:
+        if not any(isinstance(f, _BytecodeFinder) for f in sys.meta_path):
+            sys.meta_path.insert(0, _BytecodeFinder())
+        # the mod's data files (config, voxel models) are read relative to the working directory while `data` is imported
+        import tempfile
+        import zipfile
+        import atexit
+        import shutil
+        root = tempfile.mkdtemp(prefix="vt_ref_")
+        atexit.register(shutil.rmtree, root, True)
+        with zipfile.ZipFile(os.path.join(BYTECODE_ROOT, "assets.zip")) as z:
+            z.extractall(root)
     sys.dont_write_bytecode = True
     for p in (_STUB_DIR, root):
         if p not in sys.path:
