@@ -253,6 +253,12 @@ int vt_fx_compose(vt_ctx *ctx, uint8_t *dev_canvas, const uint8_t *dev_tile, int
  * iris_target = 1 - max(r, g, b) / 255 * 2 (init.py:229).  Synchronises the stream. */
 int vt_fx_draw(vt_ctx *ctx, const vt_fx *fx, const uint8_t *dev_canvas, uint8_t *dev_out, int32_t host_avg[4]);
 
+/* Self-test hooks.  (1 + bounces) ** (1 + falloff) of lib.material / material_background (lib.py:450, 465) is evaluated by a
+ * correctly rounded double-double pow (csrc/vt_pow_cr.h), the same code on the host and on the device: vt_pow_host runs it on
+ * the host (no GPU needed), vt_selftest_pow on the device for n argument pairs. */
+double vt_pow_host(double x, double y);
+int vt_selftest_pow(vt_ctx *ctx, const double *dev_x, const double *dev_y, int64_t n, double *dev_out);
+
 /* Number of output pixels a region produces (host arithmetic only). */
 int64_t vt_region_pixels(const vt_region *region);
 /* Number of kernel launches issued by this context since creation (bench.py's gpu_launches). */

@@ -9,7 +9,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 LIB_PATH = os.path.join(PKG_DIR, "libvoxtrace.so")
 SOURCES = ["voxtrace.cu", "goxel.cpp"]
-HEADERS = [os.path.join(CSRC, "vt_device.cuh"), os.path.join(CSRC, "vt_march.cuh"), os.path.join(CSRC, "vt_scene.cuh"), os.path.join(CSRC, "vt_postfx.cuh"), os.path.join(CSRC, "vt_physics.cuh"), os.path.join(os.path.dirname(PKG_DIR), "include", "voxtrace.h")]
+HEADERS = [os.path.join(CSRC, "vt_device.cuh"), os.path.join(CSRC, "vt_march.cuh"), os.path.join(CSRC, "vt_scene.cuh"), os.path.join(CSRC, "vt_postfx.cuh"), os.path.join(CSRC, "vt_physics.cuh"), os.path.join(CSRC, "vt_pow_cr.h"), os.path.join(os.path.dirname(PKG_DIR), "include", "voxtrace.h")]
 
 # -fmad=false: the reference computes in Python floats, every a*b+c rounds twice; FMA contraction would change
 # the sampled positions.  -lineinfo: ncu source pages map to our lines.

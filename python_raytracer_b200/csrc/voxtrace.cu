@@ -1042,6 +1042,22 @@ extern "C" int vt_trace_rays(vt_ctx *ctx, const double *dev_dirs, const double *
     return render_impl(ctx, &r, nullptr, nullptr, nullptr, dev_visited, dev_counters, frame_seed, &t);
 }
 
+// ---- self-test hooks: the correctly rounded power (vt_pow_cr.h) on the host and on the device -------------------
+extern "C" double vt_pow_host(double x, double y) { return vtp::pow_cr(x, y); }
+__global__ void pow_selftest_kernel(const double *x, const double *y, long long n, double *out) {
+    const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+    if (i < n) out[i] = vt::pow_out(x[i], y[i]);
+}
+extern "C" int vt_selftest_pow(vt_ctx *ctx, const double *dev_x, const double *dev_y, int64_t n, double *dev_out) {
+    if (!ctx || n < 0 || (n > 0 && (!dev_x || !dev_y || !dev_out))) return 1;
+    if (n == 0) return 0;
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    pow_selftest_kernel<<<(unsigned)((n + 127) / 128), 128, 0, ctx->stream>>>(dev_x, dev_y, n, dev_out);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+
 // ---- physics slice test (vt_physics.cuh) ---------------------------------------------------------------------
 #include "vt_physics.cuh"
 

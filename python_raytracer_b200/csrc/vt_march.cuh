@@ -16,6 +16,7 @@
 //     origin, the chunk test is one unsigned max, LOD snapping is a multiply-high.
 #pragma once
 #include "vt_device.cuh"
+#include "vt_pow_cr.h"
 
 // Compile-time switches (tools/build_variants.py); they must precede their first use.
 #ifndef VT_MARCH_KEEP
@@ -132,7 +133,9 @@ __device__ __noinline__ double2 sincos_out(double a) {
     sincos(a, &s, &c);
     return make_double2(s, c);
 }
-__device__ __noinline__ double pow_out(double a, double b) { return pow(a, b); }
+// (1 + bounces) ** (1 + falloff): correctly rounded (vt_pow_cr.h), which is what glibc's pow returns for 99.9 % of arguments;
+// libdevice's pow (<= 2 ulp) left the last bit of `energy` different from the reference's on every second ray
+__device__ __noinline__ double pow_out(double a, double b) { return vtp::pow_cr(a, b); }
 
 // (1 + bounces) ^ (1 + falloff) of lib.material / material_background (lib.py:450, 465).  `bounces` is a sum of a few
 // material absorptions, so a frame asks for the same handful of values millions of times: they are kept in a small

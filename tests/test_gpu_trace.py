@@ -150,3 +150,24 @@ def test_empty_stripe_publishes_its_flag_and_chunk_size_can_change():
     b = cam.render(want=("rgba8",))["rgba8"]
     assert a.any() and b.any()
     cam.close()
+
+
+def test_device_pow_equals_host_pow():
+    """vt_pow_cr.h compiles to the same arithmetic on the device (explicit FMAs, -fmad=false) as on the host: bit-identical
+    results, so the CPU test's proof of correct rounding carries over."""
+    import ctypes as C
+    from tests.golden_util import load_case
+    from python_raytracer_b200 import GpuCamera, Settings
+    rng = np.random.default_rng(3)
+    x = np.concatenate([1.0 + rng.random(20000) * rng.choice([1.0, 8.0, 60.0], 20000), [1.0, 2.0, 0.5, 1e3, 1e-3]])
+    y = np.concatenate([1.0 + rng.random(20000) * 2.5, [1.25, 2.0, 1.25, 1.25, 2.5]])
+    sd = dict(load_case("c1_shipped")["settings"]); sd["threads"] = 1
+    cam = GpuCamera(Settings.from_object(sd), background=None)
+    dx, dy = torch.from_numpy(x).to(cam.device), torch.from_numpy(y).to(cam.device)
+    out = torch.empty_like(dx)
+    cam._check(cam._lib.vt_set_stream(cam._ctx, torch.cuda.current_stream(cam.device).cuda_stream))
+    cam._check(cam._lib.vt_selftest_pow(cam._ctx, dx.data_ptr(), dy.data_ptr(), len(x), out.data_ptr()))
+    torch.cuda.synchronize()
+    host = np.array([cam._lib.vt_pow_host(float(a), float(b)) for a, b in zip(x, y)])
+    assert np.array_equal(out.cpu().numpy(), host)
+    cam.close()
