@@ -26,6 +26,9 @@ def test_struct_sizes_match_header():
     assert C.sizeof(abi.VtSettings) == 8 * 4 + 12 * 8
     assert C.sizeof(abi.VtMaterial) == 8 * 8
     assert C.sizeof(abi.VtRegion) == 8 * 4 + 8 + 8
+    assert C.sizeof(abi.VtObject) == 8 + 13 * 4 + 4               # pointer, size / mins / maxs / angle, reserved (+ padding)
+    assert C.sizeof(abi.VtPhysObject) == 8 + 16 * 4               # pointer, grid_lo / grid_dims / size / mins / angle, reserved
+    assert C.sizeof(abi.VtFx) == 6 * 4 + 6 * 8
 
 
 def test_no_cuda_means_loud_failure():
