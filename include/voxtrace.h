@@ -153,6 +153,27 @@ typedef struct {
 int vt_slice_collide(vt_ctx *ctx, const vt_phys_object *self, const vt_phys_object *other, const int32_t lo[3], const int32_t hi[3],
                      const int32_t vel_dir[3], double friction_scale, uint64_t seed, double inout_sums[2], int32_t *out_blocked);
 
+/* Allocation-free variant of vt_slice_collide.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  Same test, same kernels, same results; what differs:
+ *   - the per-cell scratch lives in a file-scope `static __device__` array of the library: at most
+ *     VT_STATIC_SLICE_MAX_CELLS slice cells per call (larger slices are rejected with an error -- use vt_slice_collide),
+ *     1 114 112 bytes that every GPU which loads the library holds until the process exits;
+ *   - inputs and outputs are the caller's: dev_materials = DEVICE pointer to vt_phys_material rows 0..n (what
+ *     vt_set_phys_materials would have uploaded), dev_inout = DEVICE pointer to 3 doubles {friction sum, elasticity sum,
+ *     blocked}: the two sums are read, continued and written back, blocked is written as 1.0 / 0.0;
+ *   - the call only enqueues two kernels on the context's stream (it does not synchronise and copies nothing): the
+ *     result is in dev_inout once the stream has reached that point.  No cudaMalloc / cudaFree / allocating library call
+ *     is made; the first call on a device looks the scratch address up with cudaGetSymbolAddress (do that call before
+ *     starting a graph capture).
+ * Every call on a GPU shares the one array, which keeps the last call's contents (nothing in it needs clearing: every
+ * cell a call reads it has written first).  Calls that overlap on the GPU -- two streams, two contexts on one device --
+ * race on it: serialise them. */
+#define VT_STATIC_SLICE_MAX_CELLS 65536
+int vt_slice_collide_static(vt_ctx *ctx, const vt_phys_object *self, const vt_phys_object *other, const int32_t lo[3],
+                            const int32_t hi[3], const int32_t vel_dir[3], double friction_scale, uint64_t seed,
+                            const vt_phys_material *dev_materials, double *dev_inout);
+
 /* Goxel text model -> voxel list, the parser rules of Sprite.load (data.py:271-289): single-space separated
  * "x y z rrggbb" lines, non-numeric lines skipped, colours looked up in `keys` (n_keys strings; unknown ones are
  * dropped), position (size_x - x, z, y).  Returns malloc'ed arrays in FILE ORDER (later entries override earlier

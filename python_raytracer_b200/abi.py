@@ -10,6 +10,7 @@ SETTINGS_INT = ("width", "height", "samples", "static_noise", "chunk_size", "chu
 SETTINGS_F64 = ("shutter", "falloff", "dof", "dist_min", "dist_max", "max_light", "max_bounces",
                 "lod_bounces", "lod_samples", "lod_random", "lod_edge", "proportions")
 RAY_RECORD = 16
+STATIC_SLICE_MAX_CELLS = 65536
 TRACE_RECORD = 20
 
 EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set_stream", "vt_sync",
@@ -18,7 +19,7 @@ EXPORTS = ("vt_create", "vt_destroy", "vt_last_error", "vt_abi_version", "vt_set
            "vt_launch_count", "vt_build_flags", "vt_build_world", "vt_update_region", "vt_goxel_parse", "vt_free",
            "vt_shared_alloc", "vt_shared_free", "vt_ipc_export", "vt_ipc_open", "vt_ipc_close", "vt_set_frame_target",
            "vt_stream_wait_flags", "vt_stream_signal_flags", "vt_stream_signal_flags_on", "vt_wait_status", "vt_copy_to_host", "vt_fx_compose", "vt_fx_draw",
-           "vt_wait_status_peek", "vt_pow_host", "vt_selftest_pow", "vt_set_phys_materials", "vt_slice_collide", "vt_set_tuning", "vt_clear_world", "vt_trace_rays", "vt_set_visited_peer")
+           "vt_wait_status_peek", "vt_pow_host", "vt_selftest_pow", "vt_set_phys_materials", "vt_slice_collide", "vt_slice_collide_static", "vt_set_tuning", "vt_clear_world", "vt_trace_rays", "vt_set_visited_peer")
 
 
 class VtSettings(C.Structure):
@@ -116,6 +117,8 @@ def load(path: str | None = None):
         "vt_set_phys_materials": (C.c_int, [vp, vp, i32]),
         "vt_slice_collide": (C.c_int, [vp, C.POINTER(VtPhysObject), C.POINTER(VtPhysObject), C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                        C.POINTER(C.c_int32), C.c_double, u64, C.POINTER(C.c_double), C.POINTER(C.c_int32)]),
+        "vt_slice_collide_static": (C.c_int, [vp, C.POINTER(VtPhysObject), C.POINTER(VtPhysObject), C.POINTER(C.c_int32),
+                                              C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_double, u64, vp, vp]),
         "vt_set_tuning": (C.c_int, [vp, C.c_char_p, i32]),
         "vt_clear_world": (C.c_int, [vp]),
         "vt_trace_rays": (C.c_int, [vp, vp, vp, i64, vp, vp, vp, u64]),

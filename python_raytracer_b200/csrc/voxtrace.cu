@@ -1115,6 +1115,66 @@ extern "C" int vt_slice_collide(vt_ctx *ctx, const vt_phys_object *self, const v
     return 0;
 }
 
+// ---- allocation-free variant of the slice test ---------------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  vt_slice_collide takes its per-cell scratch (one
+// flag byte + two fp64 products per cell) from grow-only cudaMalloc'ed buffers; here the scratch is this file-scope array,
+// VT_STATIC_SLICE_MAX_CELLS cells = 1 114 112 bytes held by every GPU that loads the library until the process exits.
+// In host code `vt_static_slice_scratch` is a host-side stand-in, not a device address: the address is looked up once per
+// device with cudaGetSymbolAddress (that device current) and that pointer goes to the kernels.
+static __device__ __align__(256) unsigned char vt_static_slice_scratch[(size_t)VT_STATIC_SLICE_MAX_CELLS * (sizeof(double2) + 1)];
+static unsigned char *g_static_scratch_addr[64];            // per CUDA device ordinal, resolved on first use
+
+extern "C" int vt_slice_collide_static(vt_ctx *ctx, const vt_phys_object *self, const vt_phys_object *other, const int32_t lo[3],
+                                       const int32_t hi[3], const int32_t vel_dir[3], double friction_scale, uint64_t seed,
+                                       const vt_phys_material *dev_materials, double *dev_inout) {
+    if (!ctx || !self || !other || !lo || !hi || !vel_dir || !dev_materials || !dev_inout) return 1;
+    if (ctx->device < 0 || ctx->device >= 64) return fail(ctx, "vt_slice_collide_static: device ordinal out of range");
+    vtphys::SliceArgs a;
+    memset(&a, 0, sizeof a);
+    a.self = *self; a.other = *other;
+    long long n_cells = 1;
+    for (int k = 0; k < 3; k++) {
+        if (hi[k] < lo[k]) n_cells = 0;
+        a.lo[k] = lo[k]; a.n[k] = hi[k] < lo[k] ? 0 : hi[k] - lo[k] + 1; a.dir[k] = vel_dir[k];
+        n_cells *= a.n[k];
+    }
+    if (n_cells > VT_STATIC_SLICE_MAX_CELLS)
+        return fail(ctx, "vt_slice_collide_static: slice larger than VT_STATIC_SLICE_MAX_CELLS (65536) cells; use vt_slice_collide");
+    const vt_phys_object *both[2] = {self, other};
+    for (int k = 0; k < 2; k++) {
+        if (!both[k]->dev_grid) return fail(ctx, "vt_slice_collide_static: object without a voxel grid");
+        for (int a2 = 0; a2 < 3; a2++) {
+            if (both[k]->size[a2] <= 0 || both[k]->grid_dims[a2] <= 0) return fail(ctx, "vt_slice_collide_static: sprite size / grid dims must be positive");
+            if (both[k]->angle[a2] < 0 || both[k]->angle[a2] > 3) return fail(ctx, "vt_slice_collide_static: angle must be 0..3");
+        }
+    }
+    a.scale = friction_scale; a.seed_lo = (uint32_t)seed; a.seed_hi = (uint32_t)(seed >> 32);
+    VT_CHECK(ctx, cudaSetDevice(ctx->device));
+    if (!g_static_scratch_addr[ctx->device]) {               // once per device, with that device current
+        void *ptr = nullptr;
+        VT_CHECK(ctx, cudaGetSymbolAddress(&ptr, vt_static_slice_scratch));
+        if (!ptr) return fail(ctx, "vt_slice_collide_static: cudaGetSymbolAddress returned a null address");
+        g_static_scratch_addr[ctx->device] = static_cast<unsigned char *>(ptr);
+    }
+    unsigned char *base = g_static_scratch_addr[ctx->device];
+    double2 *contrib = reinterpret_cast<double2 *>(base);                                     // [MAX] 16-byte aligned (base is 256-aligned)
+    uint8_t *flag = base + (size_t)VT_STATIC_SLICE_MAX_CELLS * sizeof(double2);               // [MAX]
+    // Nothing in the scratch has to start at zero: slice_cells_kernel writes flag[i] and contrib[i] for every i < n_cells
+    // before slice_sum_kernel reads them, so the previous call's contents are never seen.
+    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
+    if (n_cells > 0) {
+        long long want = (n_cells + 255) / 256;
+        const int grid = (int)(want < (long long)sms * 8 ? want : (long long)sms * 8);
+        vtphys::slice_cells_kernel<<<grid, 256, 0, ctx->stream>>>(a, reinterpret_cast<const double *>(dev_materials), n_cells, flag, contrib);
+        ctx->launches++;
+    }
+    vtphys::slice_sum_kernel<<<1, 1024, 0, ctx->stream>>>(flag, contrib, n_cells, dev_inout);
+    ctx->launches++;
+    VT_CHECK(ctx, cudaGetLastError());
+    return 0;
+}
+
 // ---- post-FX (vt_postfx.cuh) ------------------------------------------------------------------------------
 #include "vt_postfx.cuh"
 
