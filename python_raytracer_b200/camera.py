@@ -380,10 +380,11 @@ class GpuCamera:
                     res[name] = torch.empty(shape + tail, dtype=dt, device=self.device)
                 ptr[name] = res[name].data_ptr()
         vis = self._visited if visited_out is None else visited_out
-        if clear:
-            if visited_out is None:
+        if clear:                      # only what this call hands out: each zero_() is a kernel launch inside the frame
+            if visited_out is None and "visited" in want:
                 self._visited.zero_()
-            self._counters.zero_()
+            if "counters" in want:
+                self._counters.zero_()
         self._check(self._lib.vt_render(self._ctx, C.byref(reg), ptr.get("rgba8"), ptr.get("mean"), ptr.get("ray0"),
                                         vis.data_ptr() if "visited" in want else None,
                                         self._counters.data_ptr() if "counters" in want else None,

@@ -25,6 +25,9 @@ _FIELDS = {
 }
 
 
+_SORTED_FIELDS = tuple(sorted(_FIELDS))
+
+
 class Settings:
     """Attribute bag with the reference's names.  Derived fields follow data.py:64-68."""
 
@@ -82,4 +85,4 @@ class Settings:
         return v
 
     def key(self):
-        return tuple((n, getattr(self, n)) for n in sorted(_FIELDS))
+        return tuple(getattr(self, n) for n in _SORTED_FIELDS)
