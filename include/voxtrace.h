@@ -61,7 +61,7 @@ int vt_abi_version(void);
  * bit 1 = phase-trip instrumentation (-DVT_TRIPS=1, tools/kbench.py).  0 for the product build. */
 int vt_build_flags(void);
 /* Scheduling knobs of the render kernel for A/B measurements (tools/kbench.py): "runs" 0/1 brick-local loops, "powtab"
- * 0/1 memoised falloff power, "refill" 1..32 idle lanes that trigger a refill, "group" 1..32 lanes per pixel of a packet,
+ * 0/1 memoised falloff power, "refill" 1..32 idle lanes that trigger a refill, "group" 1..32 lanes per pixel of a packet, "buildrows" 0 / 2 / 4 rows per thread of the wide world-build kernel (0: off),
  * "debug" 0/1.  None changes a result and the product never calls it (nothing is read from the environment). */
 int vt_set_tuning(vt_ctx *ctx, const char *key, int value);
 /* Use an existing CUDA stream (cudaStream_t, e.g. torch's current stream) instead of the context's own. */

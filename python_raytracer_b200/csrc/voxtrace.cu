@@ -88,6 +88,7 @@ struct vt_ctx {
     int brick_runs = 1;                                             // VT_RUNS=0 disables empty-brick runs (A/B)
     int refill_min = 32;                                            // vt_set_tuning("refill")
     int group_max = 1;                                              // vt_set_tuning("group"): lanes per pixel of a packet
+    int build_rows = 4;                                             // vt_set_tuning("buildrows"): rows per thread of the wide world build (0: off)
     int debug = 0;
     uint32_t *visited_peer = nullptr; int visited_words = 0;        // vt_set_visited_peer
     // multi-GPU frame target (vt_set_frame_target) and the status word of the wait kernel
@@ -164,6 +165,7 @@ extern "C" int vt_set_tuning(vt_ctx *ctx, const char *key, int value) {
     else if (k == "powtab") ctx->pow_tab_on = value != 0;           // 0: no memoised falloff power
     else if (k == "refill") { if (value < 1 || value > 32) return fail(ctx, "vt_set_tuning: refill must be 1..32"); ctx->refill_min = value; }
     else if (k == "group") { if (value < 1 || value > 32) return fail(ctx, "vt_set_tuning: group must be 1..32"); ctx->group_max = value; }
+    else if (k == "buildrows") { if (value != 0 && value != 2 && value != 4) return fail(ctx, "vt_set_tuning: buildrows must be 0, 2 or 4"); ctx->build_rows = value; }
     else if (k == "debug") ctx->debug = value;
     else return fail(ctx, "vt_set_tuning: unknown key");
     return 0;
@@ -506,6 +508,36 @@ extern "C" int vt_upload_dense(vt_ctx *ctx, const uint8_t *dev_cells) {
     return 0;
 }
 
+// World cells of the box [l, l + e) from the object list: the wide kernel (16 cells x 4 rows per thread, vt_scene.cuh) when
+// rows are multiples of 16 cells and 16-byte aligned, build_cells_kernel otherwise.
+static void launch_build_cells(vt_ctx *ctx, const vt_object *d_objs, const vt_object *h_objs, int n, const int l[3], const int e[3], uint8_t *dev_cells) {
+    bool rotated = false;                                    // cells of rotated objects go cell by cell: build_cells_kernel does that inline
+    for (int k = 0; k < n; k++) rotated = rotated || (h_objs[k].angle[0] | h_objs[k].angle[1] | h_objs[k].angle[2]) != 0;
+    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
+    const int ny = ctx->dims[1], nz = ctx->dims[2];
+    const long long rows = (long long)e[0] * e[1];
+    const bool wide = ctx->build_rows > 0 && !rotated && nz % 16 == 0 && l[2] % 16 == 0 && e[2] % 16 == 0 && e[2] > 0 && rows > 0 &&
+                      (reinterpret_cast<uintptr_t>(dev_cells) & 15u) == 0 && rows * (e[2] / 16) < (1LL << 31);
+    if (wide) {
+        const int R = ctx->build_rows, chunks = e[2] / 16;
+        const long long items = ((rows + R - 1) / R) * chunks, want = (items + 255) / 256;
+        const int grid = (int)(want < (long long)sms * 16 ? want : (long long)sms * 16);
+        const unsigned long long mc = chunks > 1 ? ~0ull / (unsigned)chunks + 1ull : 0ull, me = e[1] > 1 ? ~0ull / (unsigned)e[1] + 1ull : 0ull;
+        if (R == 2)
+            build_cells16_kernel<2><<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ny, nz, l[0], l[1], l[2],
+                                                                   e[0], e[1], chunks, mc, me, dev_cells);
+        else
+            build_cells16_kernel<4><<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ny, nz, l[0], l[1], l[2],
+                                                                   e[0], e[1], chunks, mc, me, dev_cells);
+        return;
+    }
+    const long long total = rows * ((e[2] + 7) / 8);
+    long long want = (total + 255) / 256;
+    const int grid = (int)(want < (long long)sms * 32 ? (want > 0 ? want : 1) : (long long)sms * 32);
+    build_cells_kernel<<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ny, nz, l[0], l[1], l[2], e[0], e[1], e[2],
+                                                      dense_vec(ctx, dev_cells), dev_cells);
+}
+
 extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t *dev_cells) {
     if (!ctx || !dev_cells || n < 0 || (n && !objs)) return 1;
     if (!ctx->have_world) return fail(ctx, "vt_build_world: no world (vt_set_world)");
@@ -513,12 +545,8 @@ extern "C" int vt_build_world(vt_ctx *ctx, const vt_object *objs, int n, uint8_t
     VT_CHECK(ctx, cudaSetDevice(ctx->device));
     vt_object *d_objs = nullptr;
     if (int rc = stage_objects(ctx, objs, n, &d_objs)) return rc;
-    const long long total = (long long)ctx->dims[0] * ctx->dims[1] * ((ctx->dims[2] + 7) / 8);
-    const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
-    long long want = (total + 255) / 256;
-    int grid = (int)(want < (long long)sms * 32 ? want : (long long)sms * 32);
-    build_cells_kernel<<<grid, 256, 0, ctx->stream>>>(d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[1], ctx->dims[2], 0, 0,
-                                                      0, ctx->dims[0], ctx->dims[1], ctx->dims[2], dense_vec(ctx, dev_cells), dev_cells);
+    const int l0[3] = {0, 0, 0};
+    launch_build_cells(ctx, d_objs, objs, n, l0, ctx->dims, dev_cells);
     ctx->launches++;
     VT_CHECK(ctx, cudaGetLastError());
     VT_CHECK(ctx, cudaStreamSynchronize(ctx->stream));
@@ -554,12 +582,8 @@ extern "C" int vt_update_region(vt_ctx *ctx, const vt_object *objs, int n, uint8
     if (int rc = scene_scratch(ctx, 2, (size_t)m * sizeof(uint32_t), &p2)) return rc;
     uint8_t *d_flags = static_cast<uint8_t *>(p1);
     uint32_t *d_slots = static_cast<uint32_t *>(p2);
-    const long long total = (long long)e[0] * e[1] * ((e[2] + 7) / 8);
     const int sms = ctx->sm_count > 0 ? ctx->sm_count : 148;
-    long long want = (total + 255) / 256;
-    build_cells_kernel<<<(int)(want < (long long)sms * 32 ? want : (long long)sms * 32), 256, 0, ctx->stream>>>(
-        d_objs, n, ctx->origin[0], ctx->origin[1], ctx->origin[2], ctx->dims[1], ctx->dims[2], l[0], l[1], l[2], e[0], e[1], e[2],
-        dense_vec(ctx, dev_cells), dev_cells);
+    launch_build_cells(ctx, d_objs, objs, n, l, e, dev_cells);
     region_flags_kernel<<<(m + 3) / 4 < sms * 16 ? (m + 3) / 4 : sms * 16, 128, 0, ctx->stream>>>(
         dev_cells, ctx->dims[0], ctx->dims[1], ctx->dims[2], b0[0], b0[1], b0[2], rb[0], rb[1], rb[2], d_flags);
     ctx->launches += 2;

@@ -135,6 +135,162 @@ __global__ void __launch_bounds__(256) build_cells_kernel(const vt_object *__res
     }
 }
 
+// ---- the same world build, wide variant -------------------------------------------------------------------------------
+// build_cells_kernel spends ~200 warp instructions per 32 runs of 8 cells: a fifth in the two integer divisions of the index
+// decode, the rest in re-reading the object record and in one short, latency-exposed load chain per thread (ncu, round 2:
+// issue slots 70 % busy, long_scoreboard 5 of 12 stall cycles, 1.24 TB/s).  This variant serves worlds whose rows are
+// multiples of 16 cells and 16-byte aligned: one thread makes 16 cells of ROWS consecutive rows (same z, y counting up), so
+// that the decode (two multiply-high divisions with host-made multipliers) and every object record (four 16-byte loads) are
+// paid once per ROWS x 16 cells, the sprite words of all ROWS rows are requested before any is used, and rows leave as
+// 16-byte stores.  Cell values are exactly build_cells_kernel's (same object order, same pos_rotated path for the rest).
+struct ObjRegs {
+    const uint8_t *sp;
+    int s0, s1, s2, mn0, mn1, mn2, mx0, mx1, mx2, a0, a1, a2;
+};
+__device__ __forceinline__ ObjRegs load_object(const vt_object *__restrict__ o) {      // 64-byte records, 16-byte aligned
+    const int4 q0 = __ldg(reinterpret_cast<const int4 *>(o)), q1 = __ldg(reinterpret_cast<const int4 *>(o) + 1);
+    const int4 q2 = __ldg(reinterpret_cast<const int4 *>(o) + 2), q3 = __ldg(reinterpret_cast<const int4 *>(o) + 3);
+    ObjRegs r;
+    r.sp = reinterpret_cast<const uint8_t *>(((unsigned long long)(unsigned)q0.y << 32) | (unsigned)q0.x);
+    r.s0 = q0.z; r.s1 = q0.w; r.s2 = q1.x; r.mn0 = q1.y; r.mn1 = q1.z; r.mn2 = q1.w;
+    r.mx0 = q2.x; r.mx1 = q2.y; r.mx2 = q2.z; r.a0 = q2.w; r.a1 = q3.x; r.a2 = q3.y;
+    return r;
+}
+// floor(u / d) for u < 2^32 with m = floor(2^64 / d) + 1 (d >= 2); exact: the error term u * (m d - 2^64) stays below 2^64
+__device__ __forceinline__ unsigned div_magic(unsigned u, unsigned long long m, unsigned d) {
+    return d == 1u ? u : (unsigned)__umul64hi((unsigned long long)u, m);
+}
+
+// the 8-cell run at (wx, wy, wz0) from one object, cell by cell (rotations, box edges, sprite ends): the rare path, one
+// out-of-line copy (inlined into the unrolled row loop it cost 117 registers and 6 300 instructions).  -> {out, need}
+__device__ __noinline__ ulonglong2 object_cells8(const vt_object *__restrict__ orec, int wx, int wy, int wz0, unsigned long long out,
+                                                 unsigned long long need) {
+    const vt_object &o = *orec;
+    const int c0 = max(0, o.mins[2] - wz0), c1 = min(8, o.maxs[2] - wz0);
+    if (c0 >= c1) return make_ulonglong2(out, need);
+    const bool plain = (o.angle[0] | o.angle[1] | o.angle[2]) == 0;
+    const int bx = wx - o.mins[0], by = wy - o.mins[1], bz = wz0 - o.mins[2];
+    const int s0 = o.size[0], s1 = o.size[1], s2 = o.size[2];
+    for (int c = c0; c < c1; c++) {
+        if (!((need >> (8 * c)) & 1ull)) continue;
+        int lx = bx, ly = by, lz = bz + c;
+        if (!plain) pos_rotated(o, lx, ly, lz);
+        if ((unsigned)lx >= (unsigned)s0 || (unsigned)ly >= (unsigned)s1 || (unsigned)lz >= (unsigned)s2) continue;
+        const unsigned long long m = __ldg(o.dev_sprite + ((size_t)lx * s1 + ly) * s2 + lz);
+        if (m) { out |= m << (8 * c); need &= ~(0xffull << (8 * c)); }
+    }
+    return make_ulonglong2(out, need);
+}
+
+#ifndef VT_BC_MINB
+#define VT_BC_MINB 2                 // resident 256-thread blocks per SM the wide world build is sized for
+#endif
+template <int ROWS>
+__global__ void __launch_bounds__(256, VT_BC_MINB) build_cells16_kernel(const vt_object *__restrict__ objs, int n, int ox, int oy, int oz, int ny, int nz,
+                                                            int lx0, int ly0, int lz0, int ex, int ey, int chunks, unsigned long long m_chunks,
+                                                            unsigned long long m_ey, uint8_t *__restrict__ cells) {
+    const unsigned n_rows = (unsigned)ex * (unsigned)ey, groups = (n_rows + ROWS - 1) / ROWS;
+    const unsigned total = groups * (unsigned)chunks;                     // < 2^31 (host)
+    for (unsigned i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const unsigned g = div_magic(i, m_chunks, (unsigned)chunks), c = i - g * (unsigned)chunks;
+        const unsigned row0 = g * ROWS;
+        const unsigned x0 = div_magic(row0, m_ey, (unsigned)ey);
+        int x = (int)x0, y = (int)(row0 - x0 * (unsigned)ey);
+        const int z0 = lz0 + 16 * (int)c, wz0 = z0 + oz;
+        int wx[ROWS], wy[ROWS];
+        bool valid[ROWS];
+        unsigned long long out0[ROWS], out1[ROWS], need0[ROWS], need1[ROWS];
+#pragma unroll
+        for (int r = 0; r < ROWS; r++) {
+            valid[r] = row0 + r < n_rows;
+            wx[r] = x + lx0 + ox; wy[r] = y + ly0 + oy;
+            out0[r] = out1[r] = 0ull;
+            need0[r] = need1[r] = valid[r] ? ~0ull : 0ull;
+            if (++y == ey) { y = 0; x++; }
+        }
+        for (int k = n - 1; k >= 0; k--) {
+            unsigned long long any = 0ull;
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) any |= need0[r] | need1[r];
+            if (!any) break;
+            // quick reject on the box alone (two of the record's four words): most objects of a many-object world miss the
+            // thread's 16 cells in z, its x (rows of a thread span at most two x) or its y range
+            {
+                const int4 q1 = __ldg(reinterpret_cast<const int4 *>(objs + k) + 1), q2 = __ldg(reinterpret_cast<const int4 *>(objs + k) + 2);
+                const int mn0 = q1.y, mn1 = q1.z, mn2 = q1.w, mx0 = q2.x, mx1 = q2.y, mx2 = q2.z;
+                if (mn2 >= wz0 + 16 || mx2 <= wz0) continue;
+                if ((wx[0] < mn0 || wx[0] >= mx0) && (wx[ROWS - 1] < mn0 || wx[ROWS - 1] >= mx0)) continue;
+                if (wx[0] == wx[ROWS - 1] && (wy[ROWS - 1] < mn1 || wy[0] >= mx1)) continue;
+            }
+            const ObjRegs o = load_object(objs + k);
+            const int c0 = max(0, o.mn2 - wz0), c1 = min(16, o.mx2 - wz0);
+            if (c0 >= c1) continue;                                       // the 16 cells miss the object in z (same for every row)
+            // Word path for unrotated objects: the cells c0 <= c < c1 the object covers are sprite bytes zlo .. zlo + cnt - 1 of
+            // the row, fetched as up to three aligned 8-byte words, funnel-shifted to byte 0, moved up to cell c0 and masked
+            // to [c0, c1) -- whole chunks and the partial ones at the object's z faces alike (c0, c1 are the same for every
+            // row of the thread).
+            const int bz = wz0 - o.mn2, zlo = bz + c0, cnt = c1 - c0;
+            const bool words = (o.a0 | o.a1 | o.a2) == 0 && (reinterpret_cast<uintptr_t>(o.sp) & 7u) == 0;
+            const size_t sprite_bytes = (size_t)o.s0 * o.s1 * o.s2;
+            const unsigned long long lo_c0 = c0 >= 8 ? ~0ull : (1ull << (8 * c0)) - 1ull, lo_c1 = c1 >= 8 ? ~0ull : (1ull << (8 * c1)) - 1ull;
+            const unsigned long long hi_c0 = c0 <= 8 ? 0ull : (1ull << (8 * (c0 - 8))) - 1ull;
+            const unsigned long long hi_c1 = c1 <= 8 ? 0ull : (c1 >= 16 ? ~0ull : (1ull << (8 * (c1 - 8))) - 1ull);
+            const unsigned long long keep0 = lo_c1 & ~lo_c0, keep1 = hi_c1 & ~hi_c0;
+            // pass 1: which rows take the word path, and where; pass 2: all their loads; pass 3: merge / cell-by-cell rest
+            const unsigned long long *p[ROWS];
+            int sh[ROWS], nw[ROWS];
+            bool in_xy[ROWS], fast[ROWS];
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) {
+                const int bx = wx[r] - o.mn0, by = wy[r] - o.mn1;
+                in_xy[r] = (need0[r] | need1[r]) != 0ull && wx[r] >= o.mn0 && wx[r] < o.mx0 && wy[r] >= o.mn1 && wy[r] < o.mx1;
+                const size_t off = ((size_t)bx * o.s1 + by) * o.s2 + zlo;
+                const size_t w0 = off >> 3, wl = (off + cnt - 1) >> 3;        // first and last aligned word touched
+                fast[r] = in_xy[r] && words && (unsigned)bx < (unsigned)o.s0 && (unsigned)by < (unsigned)o.s1 && zlo >= 0 && zlo + cnt <= o.s2 &&
+                          (wl + 1) * 8 <= sprite_bytes;
+                p[r] = reinterpret_cast<const unsigned long long *>(o.sp) + w0;
+                sh[r] = (int)(off & 7) * 8;
+                nw[r] = (int)(wl - w0);
+            }
+            unsigned long long a[ROWS], b[ROWS], cw[ROWS];
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) {
+                a[r] = fast[r] ? __ldg(p[r]) : 0ull;
+                b[r] = fast[r] && nw[r] >= 1 ? __ldg(p[r] + 1) : 0ull;
+                cw[r] = fast[r] && nw[r] >= 2 ? __ldg(p[r] + 2) : 0ull;
+            }
+#pragma unroll
+            for (int r = 0; r < ROWS; r++) {
+                if (fast[r]) {
+                    const unsigned long long u0 = sh[r] ? (a[r] >> sh[r]) | (b[r] << (64 - sh[r])) : a[r];      // sprite bytes zlo .. zlo + 7
+                    const unsigned long long u1 = sh[r] ? (b[r] >> sh[r]) | (cw[r] << (64 - sh[r])) : b[r];     // zlo + 8 .. zlo + 15
+                    unsigned long long v0, v1;                                                              // the same, moved up to cell c0
+                    if (c0 == 0) { v0 = u0; v1 = u1; }
+                    else if (c0 < 8) { v0 = u0 << (8 * c0); v1 = (u1 << (8 * c0)) | (u0 >> (64 - 8 * c0)); }
+                    else if (c0 == 8) { v0 = 0ull; v1 = u0; }
+                    else { v0 = 0ull; v1 = u0 << (8 * (c0 - 8)); }
+                    const unsigned long long m0 = nonzero_bytes(v0) & need0[r] & keep0, m1 = nonzero_bytes(v1) & need1[r] & keep1;
+                    out0[r] |= v0 & m0; need0[r] &= ~m0;
+                    out1[r] |= v1 & m1; need1[r] &= ~m1;
+                } else if (in_xy[r]) {
+                    const ulonglong2 h0 = object_cells8(objs + k, wx[r], wy[r], wz0, out0[r], need0[r]);
+                    const ulonglong2 h1 = object_cells8(objs + k, wx[r], wy[r], wz0 + 8, out1[r], need1[r]);
+                    out0[r] = h0.x; need0[r] = h0.y; out1[r] = h1.x; need1[r] = h1.y;
+                }
+            }
+        }
+        x = (int)x0; y = (int)(row0 - x0 * (unsigned)ey);
+#pragma unroll
+        for (int r = 0; r < ROWS; r++) {
+            if (valid[r]) {
+                uint8_t *row_p = cells + ((size_t)(x + lx0) * ny + (y + ly0)) * nz;
+                *reinterpret_cast<uint4 *>(row_p + z0) = make_uint4((uint32_t)out0[r], (uint32_t)(out0[r] >> 32), (uint32_t)out1[r], (uint32_t)(out1[r] >> 32));
+            }
+            if (++y == ey) { y = 0; x++; }
+        }
+    }
+}
+
 // ---- dense world -> bricks ------------------------------------------------------------------------------------
 // A *task* is 32 bricks that follow each other along z: bz in [32 g, 32 g + 32) of brick column (bx, by).  Task
 // index t = (bx * nby + by) * G + g, G = ceil(nbz / 32): tasks, and the bricks inside them, are in brick-index order,
