@@ -15,7 +15,7 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-STRIPE_ROWS = int(os.environ.get("VT_STRIPE_ROWS", "8"))     # rows per interleaved stripe (tuning knob)
+STRIPE_ROWS = 8       # rows per interleaved stripe (2-16 measure the same; pass `stripe=` to the renderers to change it)
 
 
 def stripe_rows(height: int, rank: int, world: int, stripe: int = STRIPE_ROWS) -> np.ndarray:
