@@ -180,3 +180,52 @@ def test_build_cells_matches_per_cell_restatement(cs):
     assert int((got > 0).sum()) == int((fresh > 0).sum())
     assert np.array_equal(cam.download_dense().cpu().numpy(), got)
     cam.close(); cam2.close()
+
+
+@pytest.mark.parametrize("rows", [4, 2, 0])
+def test_wide_build_kernel_matches_restatement(rows):
+    """build_cells16_kernel (unrotated objects, rows that are multiples of 16 cells): 40 overlapping objects of odd sizes at
+    odd and fractional positions -- partial coverage of a thread's 16 cells at every object's z faces, sprite rows that start
+    at any byte, sprite tails, rows of a thread that straddle two x, later objects overriding earlier ones -- against the
+    per-cell rule painted with numpy; buildrows 4 / 2 (wide) and 0 (build_cells_kernel) give the same cells."""
+    from python_raytracer_b200.builder import SceneObject, WorldBuilder
+    rng = np.random.default_rng(5)
+    objs = []
+    for k in range(40):
+        size = tuple(int(v) for v in rng.integers(1, 40, 3))
+        pos = tuple(float(v) for v in (rng.integers(-60, 60, 3) + rng.choice([0.0, 0.5, 0.25], 3)))
+        spr = (rng.random(size) < 0.5).astype(np.uint8) * np.uint8(1 + k % 7)
+        objs.append(SceneObject(sprite=spr, pos=pos, rot=(0.0, 0.0, 0.0)))
+    objs.append(SceneObject(sprite=np.full((3, 3, 70), 3, np.uint8), pos=(5.0, 5.0, -2.0)))       # long along z: whole chunks
+    cam = _camera(16)
+    cam._check(cam._lib.vt_set_tuning(cam._ctx, b"buildrows", rows))
+    wb = WorldBuilder(cam)
+    cells = wb.build(objs, MATS[:8]).cpu().numpy()
+    assert cells.shape[2] % 16 == 0
+    exp = np.zeros_like(cells)
+    for o in objs:
+        mins, maxs = o.box()
+        n = [maxs[a] - mins[a] for a in range(3)]
+        if min(n) <= 0:
+            continue
+        sub = o.sprite[:n[0], :n[1], :n[2]]
+        lo = [mins[a] - int(wb.origin[a]) for a in range(3)]
+        view = exp[lo[0]:lo[0] + n[0], lo[1]:lo[1] + n[1], lo[2]:lo[2] + n[2]]
+        view[sub > 0] = sub[sub > 0]
+    assert np.array_equal(cells, exp)
+    # a region update through the same dispatch: one object moves by an odd amount
+    objs[7].pos = (objs[7].pos[0] + 3.0, objs[7].pos[1] - 2.5, objs[7].pos[2] + 5.0)
+    wb.update(objs, [objs[7]])
+    cam2 = _camera(16)
+    wb2 = WorldBuilder(cam2)
+    order = [o for o in objs if o is not objs[7]] + [objs[7]]
+    fresh = wb2.build(order, MATS[:8]).cpu().numpy()
+    got = wb.cells.cpu().numpy()
+    lo = np.minimum(wb.origin, wb2.origin)
+    hi = np.maximum(wb.origin + np.array(got.shape), wb2.origin + np.array(fresh.shape))
+    a, b = np.zeros(tuple(hi - lo), np.uint8), np.zeros(tuple(hi - lo), np.uint8)
+    o1, o2 = (wb.origin - lo).astype(int), (wb2.origin - lo).astype(int)
+    a[o1[0]:o1[0] + got.shape[0], o1[1]:o1[1] + got.shape[1], o1[2]:o1[2] + got.shape[2]] = got
+    b[o2[0]:o2[0] + fresh.shape[0], o2[1]:o2[1] + fresh.shape[1], o2[2]:o2[2] + fresh.shape[2]] = fresh
+    assert np.array_equal(a, b)
+    cam.close(); cam2.close()
