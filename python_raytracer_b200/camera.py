@@ -294,8 +294,9 @@ class GpuCamera:
         if tuple(t.shape) != tuple(v // cs for v in self._world_shape):
             raise VoxtraceError("chunk_res shape %s does not match world %s / chunk_size %d" % (t.shape, self._world_shape, cs))
         self._check(self._lib.vt_set_chunk_table(self._ctx, t.ctypes.data, t.size))
+        if getattr(self, "_chunk_res_shape", None) != t.shape:       # same grid: the visited words keep their size (cleared per render)
+            self._visited = None
         self._chunk_res_shape = t.shape
-        self._visited = None
 
     def download_dense(self):
         """The world held in bricks as a dense [nx, ny, nz] u8 CUDA tensor (inverse of ``set_world_dense``)."""
