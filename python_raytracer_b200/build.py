@@ -17,14 +17,19 @@ NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", 
               "-shared", "-Xcompiler", "-fPIC", "-lz"]
 
 
+RENDER_KERNEL_FILES = ["vt_march.cuh", "vt_device.cuh", "vt_pow_cr.h"]
+
+
 def kernel_source_sha256() -> str:
-    """sha256 over the CUDA / C++ sources and the ABI header: ties a committed ncu capture to the kernel it was taken
-    from (profiles/r*_traffic.json carry it, bench.py reports `traffic_stale` when it differs)."""
+    """sha256 over the sources of the render kernel (vt_march.cuh with its launch bounds, vt_device.cuh, vt_pow_cr.h) and the
+    nvcc flags: ties a committed ncu capture of render_persistent to the kernel it was taken from (profiles/r*_traffic.json
+    carry it, bench.py reports `traffic_stale` when it differs).  Host code and the other kernels are not part of it."""
     import hashlib
     h = hashlib.sha256()
-    for path in sorted([os.path.join(CSRC, s) for s in SOURCES] + HEADERS):
-        with open(path, "rb") as f:
-            h.update(os.path.basename(path).encode() + b"\0" + f.read())
+    h.update(" ".join(NVCC_FLAGS).encode())
+    for name in RENDER_KERNEL_FILES:
+        with open(os.path.join(CSRC, name), "rb") as f:
+            h.update(name.encode() + b"\0" + f.read())
     return h.hexdigest()
 
 
